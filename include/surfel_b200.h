@@ -1,0 +1,110 @@
+/* surfel_b200 -- C ABI of the B200-native 2D-Gaussian (surfel) differentiable rasterizer.
+ *
+ * Drop-in boundary for VINGS-Mono's rasterizer extension.  These entry points are what the
+ * reference's torch glue (submodules/diff-surfel-rasterization/rasterize_points.cu) would call
+ * instead of CudaRasterizer::Rasterizer::{forward,backward,markVisible} and ADAM::adamUpdate:
+ *
+ *   sb200_forward_begin + sb200_forward_finish  <->  RasterizeGaussiansCUDA          rasterize_points.cu:41-149
+ *                                                    Rasterizer::forward             cuda_rasterizer/rasterizer_impl.cu:305-478
+ *   sb200_backward                              <->  RasterizeGaussiansBackwardCUDA  rasterize_points.cu:151-256
+ *                                                    Rasterizer::backward            cuda_rasterizer/rasterizer_impl.cu:482-599
+ *   sb200_mark_visible                          <->  markVisible                     rasterize_points.cu:258-277
+ *   sb200_adam_update                           <->  adamUpdate                      rasterize_points.cu:281-306, cuda_rasterizer/adam.cu:40-67
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous fp32/int32/u8 data unless it says "host";
+ *   - the library never allocates or frees device memory: workspaces are caller-allocated from the
+ *     sizes returned by the *_bytes queries (the reference grows torch tensors through
+ *     std::function<char*(size_t)> callbacks, rasterizer.h:32-35; here the caller does the resize
+ *     between forward_begin and forward_finish, which is the only point a size is data dependent);
+ *   - every launch goes to the explicit `stream` (the reference uses the legacy default stream);
+ *   - the only host synchronisation is inside sb200_forward_begin (one 8-byte D2H read of the pair
+ *     count R; the reference blocks twice, rasterizer_impl.cu:391,439);
+ *   - return value 0 = ok, non-zero = error, message via sb200_last_error(); nothing is thrown.
+ *   - matrices are the reference's: 16 floats, the row-major torch tensor holding the transposed
+ *     (column-major-read) world->view and full projection matrices (auxiliary.h:91-130).
+ */
+#ifndef SURFEL_B200_H
+#define SURFEL_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ABI version of this header (bumped on any signature change). */
+int sb200_abi_version(void);
+/* Message of the last failing call on this thread ("" if none). */
+const char* sb200_last_error(void);
+
+/* ---- workspace sizes ------------------------------------------------------------------------ */
+/* per-surfel workspace (reference: GeometryState, rasterizer_impl.h:29-44); must persist forward->backward */
+size_t sb200_geom_bytes(int64_t P);
+/* per-image workspace: tile ranges + per-pixel final T/M1/M2 and contributor counts
+ * (reference: ImageState, rasterizer_impl.h:46-65); must persist forward->backward */
+size_t sb200_image_bytes(int W, int H);
+/* sort scratch for R (tile,surfel) pairs (reference: BinningState, rasterizer_impl.h:86-97); dead after forward_finish */
+size_t sb200_binning_bytes(int64_t R);
+/* per-surfel gradient accumulation scratch for the backward: 80 B * P, zeroed by the library */
+size_t sb200_grad_bytes(int64_t P);
+/* byte offsets of the inspectable arrays inside the workspaces (tests / debugging):
+ *   geom:    [0] records float4[5P]  [1] depth f32[P]  [2] tile rect u16x4[P]  [3] tiles_touched u32[P]
+ *            [4] point_offsets u32[P] (inclusive)
+ *   image:   [0] ranges uint2[tiles] [1] final T,M1,M2 f32[3HW]  [2] n_contrib,median_contrib u32[2HW]
+ *   binning: [0] keys A u64[R] (unsorted keys)  [1] keys B u64[R]  [2] values A u32[R]  [3] values B u32[R] */
+void sb200_geom_layout(int64_t P, size_t out[5]);
+void sb200_image_layout(int W, int H, size_t out[3]);
+void sb200_binning_layout(int64_t R, size_t out[4]);
+
+/* ---- forward -------------------------------------------------------------------------------- */
+/* Stage 1: per-surfel preprocess (ray-splat transform, AABB, radius, tile rect) + prefix sum of the
+ * tile counts.  Writes radii[P] (int32) and the geometry workspace, then synchronises `stream` once to
+ * return the number of (tile,surfel) pairs in *num_rendered_host (host pointer, pinned preferred). */
+int sb200_forward_begin(int P, int W, int H,
+                        const float* means3D,    /* [P,3] */
+                        const float* scales,     /* [P,2] */
+                        const float* rotations,  /* [P,4] (w,x,y,z) */
+                        const float* opacities,  /* [P]   */
+                        const float* colors,     /* [P,3] colors_precomp */
+                        const float* viewmatrix, const float* projmatrix,
+                        void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream);
+
+/* Stage 2: key duplication, onesweep radix sort, tile ranges, per-tile blend.
+ * point_list[R] (u32) receives the sorted surfel ids and must persist until the backward.
+ * out_color [3,H,W]; out_others [7,H,W] = depth, alpha, normal xyz (view space), median depth, distortion. */
+int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg /* [3] */,
+                         void* geom_ws, void* binning_ws, uint32_t* point_list, void* image_ws,
+                         float* out_color, float* out_others, void* stream);
+
+/* ---- backward ------------------------------------------------------------------------------- */
+/* All dL_d* outputs and scores are fully written (no pre-zeroing needed).  dL_dtransMat may be NULL.
+ * pixel_mask: u8/bool [H*W]; masked-out pixels contribute no gradient and no score. */
+int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                   const float* means3D, const float* scales, const float* rotations,
+                   const float* viewmatrix, const float* projmatrix, const int* radii,
+                   const void* geom_ws, const uint32_t* point_list, const void* image_ws,
+                   const float* out_color, const float* out_others,
+                   const float* dL_dout_color /* [3,H,W] */, const float* dL_dout_others /* [7,H,W] */,
+                   const uint8_t* pixel_mask, void* grad_ws,
+                   float* dL_dmeans3D /* [P,3] */, float* dL_dmeans2D /* [P,3] */, float* dL_dcolors /* [P,3] */,
+                   float* dL_dopacity /* [P,1] */, float* dL_dscales /* [P,2] */, float* dL_drotations /* [P,4] */,
+                   float* dL_dtransMat /* [P,9] or NULL */, float* scores /* [P,2] */, void* stream);
+
+/* ---- auxiliaries exported by the same reference module -------------------------------------- */
+int sb200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present /* bool [P] */, void* stream);
+int sb200_adam_update(float* param, const float* param_grad, float* exp_avg, float* exp_avg_sq,
+                      const uint8_t* visible /* bool [N] */, float lr, float b1, float b2, float eps,
+                      uint32_t N, uint32_t M, void* stream);
+
+/* ---- building blocks exposed for parity tests ----------------------------------------------- */
+/* Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0,end_bit).  keys_in/vals_in are
+ * clobbered; scratch = sb200_binning_bytes(n) bytes whose keys A / values A arrays (see layout) ARE
+ * keys_in / vals_in.  On return keys_out/vals_out (caller buffers of n) hold the sorted pairs. */
+int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, uint64_t* keys_out, uint32_t* vals_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,185 @@
+"""Shared helpers for the parity tests: drive this package, the reference build (oracle/_ref) and the
+CPU emulation (oracle/surfel_emulation.py) on identical seeded inputs."""
+import ctypes
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_DIR = os.path.join(ROOT, "oracle", "_ref", "diff_surfel_rasterization")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def load_mine():
+    import diff_surfel_rasterization as m
+    assert os.path.dirname(m.__file__).startswith(os.path.join(ROOT, "vings-mono_b200"))
+    return m
+
+
+def load_ref():
+    """The unmodified reference extension built by oracle/build_ref.py, under an alias module name."""
+    if "ref_dsr" in sys.modules:
+        return sys.modules["ref_dsr"]
+    init = os.path.join(REF_DIR, "__init__.py")
+    if not (os.path.exists(init) and os.path.exists(os.path.join(REF_DIR, "_C.so"))):
+        return None
+    spec = importlib.util.spec_from_file_location("ref_dsr", init, submodule_search_locations=[REF_DIR])
+    mod = importlib.util.module_from_spec(spec)
+    sys.modules["ref_dsr"] = mod
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def cuda_inputs(inp):
+    return {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in inp.items()}
+
+
+def make_settings(mod, inp, mask=None):
+    W, H = inp["W"], inp["H"]
+    dev = inp["means3D"].device
+    if mask is None:
+        mask = torch.ones(H * W, dtype=torch.bool, device=dev)
+    return mod.GaussianRasterizationSettings(
+        image_height=H, image_width=W, tanfovx=inp["tanfovx"], tanfovy=inp["tanfovy"], bg=inp["bg"],
+        scale_modifier=1.0, viewmatrix=inp["viewmatrix"], projmatrix=inp["projmatrix"], sh_degree=0,
+        campos=inp["campos"], prefiltered=False, debug=False, pixel_mask=mask)
+
+
+GRAD_NAMES = ("means3D", "means2D", "colors", "opacities", "scales", "rotations", "scores")
+
+
+def run_impl(mod, inp, g_color, g_allmap, mask=None):
+    """One fwd+bwd through the public API (the call VINGS-Mono's mapper makes, gaussian_base.py:193-203).
+    Returns CPU tensors."""
+    P = inp["means3D"].shape[0]
+    dev = inp["means3D"].device
+    leaf = lambda t: t.detach().clone().requires_grad_(True)
+    means3D, colors, opac = leaf(inp["means3D"]), leaf(inp["colors"]), leaf(inp["opacities"])
+    scales, rots = leaf(inp["scales"]), leaf(inp["rotations"])
+    means2D = torch.zeros(P, 3, device=dev, requires_grad=True)
+    scores = torch.zeros(P, 2, device=dev, requires_grad=True)
+    rast = mod.GaussianRasterizer(raster_settings=make_settings(mod, inp, mask))
+    color, radii, allmap = rast(means3D=means3D, means2D=means2D, opacities=opac, shs=None, colors_precomp=colors,
+                                scales=scales, rotations=rots, cov3D_precomp=None, scores=scores)
+    torch.autograd.backward([color, allmap], [g_color.to(dev), g_allmap.to(dev)])
+    torch.cuda.synchronize()
+    out = dict(color=color.detach().cpu(), radii=radii.cpu(), allmap=allmap.detach().cpu())
+    for name, t in zip(GRAD_NAMES, (means3D, means2D, colors, opac, scales, rots, scores)):
+        out["d_" + name] = t.grad.detach().cpu() if t.grad is not None else torch.zeros_like(t).cpu()
+    return out
+
+
+def _a128(x):
+    return (x + 127) // 128 * 128
+
+
+def ref_intermediates(ref, inp):
+    """Calls the reference's _C.rasterize_gaussians and slices its opaque byte buffers with the fromChunk
+    layouts (rasterizer_impl.cu:228-301; every field 128-B aligned) -- no reference source is modified."""
+    P = inp["means3D"].shape[0]
+    W, H = inp["W"], inp["H"]
+    dev = inp["means3D"].device
+    e = torch.empty(0, device=dev)
+    R, B, color, others, radii, geom, binning, img, sample = ref._C.rasterize_gaussians(
+        inp["bg"], inp["means3D"], inp["colors"], inp["opacities"], inp["scales"], inp["rotations"], 1.0, e,
+        inp["viewmatrix"], inp["projmatrix"], inp["tanfovx"], inp["tanfovy"], H, W, e, 0, inp["campos"], False, False)
+    torch.cuda.synchronize()
+    g = geom.cpu().numpy()
+    off = 0
+    def take(buf, off, nbytes, dtype):
+        off = _a128(off)
+        return np.frombuffer(buf[off:off + nbytes].tobytes(), dtype=dtype), off + nbytes
+    depths, off = take(g, off, 4 * P, np.float32)
+    _, off = take(g, off, 3 * P, np.uint8)
+    _, off = take(g, off, 4 * P, np.int32)
+    means2D, off = take(g, off, 8 * P, np.float32)
+    transMat, off = take(g, off, 36 * P, np.float32)
+    nrm_opa, off = take(g, off, 16 * P, np.float32)
+    _, off = take(g, off, 12 * P, np.float32)
+    tiles, off = take(g, off, 4 * P, np.uint32)
+    b = binning.cpu().numpy()
+    off = 0
+    point_list, off = take(b, off, 4 * R, np.uint32)
+    vals_unsorted, off = take(b, off, 4 * R, np.uint32)
+    keys, off = take(b, off, 8 * R, np.uint64)
+    keys_unsorted, off = take(b, off, 8 * R, np.uint64)
+    im = img.cpu().numpy()
+    N = W * H
+    off = 0
+    accum, off = take(im, off, 12 * N, np.float32)
+    n_contrib, off = take(im, off, 8 * N, np.uint32)
+    ranges, off = take(im, off, 8 * N, np.uint32)
+    tiles_n = ((W + 15) // 16) * ((H + 15) // 16)
+    return dict(R=R, B=B, color=color.cpu(), allmap=others.cpu(), radii=radii.cpu().numpy(), depths=depths,
+                means2D=means2D.reshape(P, 2), transMat=transMat.reshape(P, 9), normal_opacity=nrm_opa.reshape(P, 4),
+                tiles_touched=tiles, point_list=point_list, vals_unsorted=vals_unsorted, keys=keys,
+                keys_unsorted=keys_unsorted, final_T=accum.reshape(3, N), n_contrib=n_contrib.reshape(2, N),
+                ranges=ranges.reshape(N, 2)[:tiles_n])
+
+
+def mine_intermediates(mine, inp):
+    """Drives the C ABI directly (forward_begin / forward_finish) and reads the workspaces."""
+    lib = mine._load()
+    P = inp["means3D"].shape[0]
+    W, H = inp["W"], inp["H"]
+    dev = inp["means3D"].device
+    vp = ctypes.c_void_p
+    ptr = lambda t: vp(t.data_ptr())
+    st = vp(torch.cuda.current_stream().cuda_stream)
+    geom = torch.zeros(lib.sb200_geom_bytes(P), dtype=torch.uint8, device=dev)
+    image = torch.zeros(lib.sb200_image_bytes(W, H), dtype=torch.uint8, device=dev)
+    radii = torch.zeros(P, dtype=torch.int32, device=dev)
+    count = torch.zeros(1, dtype=torch.int64).pin_memory()
+    rc = lib.sb200_forward_begin(P, W, H, ptr(inp["means3D"]), ptr(inp["scales"]), ptr(inp["rotations"]),
+                                 ptr(inp["opacities"]), ptr(inp["colors"]), ptr(inp["viewmatrix"]),
+                                 ptr(inp["projmatrix"]), ptr(geom), ptr(radii), vp(count.data_ptr()), st)
+    assert rc == 0, lib.sb200_last_error()
+    R = int(count[0])
+    binning = torch.zeros(lib.sb200_binning_bytes(R), dtype=torch.uint8, device=dev)
+    point_list = torch.zeros(max(R, 1), dtype=torch.int32, device=dev)
+    color = torch.zeros(3, H, W, device=dev)
+    others = torch.zeros(7, H, W, device=dev)
+    rc = lib.sb200_forward_finish(P, W, H, R, ptr(inp["bg"]), ptr(geom), ptr(binning), ptr(point_list), ptr(image),
+                                  ptr(color), ptr(others), st)
+    assert rc == 0, lib.sb200_last_error()
+    torch.cuda.synchronize()
+    go = (ctypes.c_size_t * 5)(); lib.sb200_geom_layout(P, go)
+    io = (ctypes.c_size_t * 3)(); lib.sb200_image_layout(W, H, io)
+    bo = (ctypes.c_size_t * 4)(); lib.sb200_binning_layout(R, bo)
+    g = geom.cpu().numpy(); im = image.cpu().numpy(); b = binning.cpu().numpy()
+    fb = lambda buf, off, n, dt: np.frombuffer(buf[off:off + n].tobytes(), dtype=dt)
+    rec = fb(g, go[0], 80 * P, np.float32).reshape(P, 20)
+    N = W * H
+    tiles_n = ((W + 15) // 16) * ((H + 15) // 16)
+    passes = (32 + _higher_msb(tiles_n) + 7) // 8
+    # after an even number of passes the sorted keys are back in buffer A, else in B
+    keys_sorted = fb(b, bo[0] if passes % 2 == 0 else bo[1], 8 * R, np.uint64)
+    vis = radii.cpu().numpy() > 0
+    return dict(R=R, color=color.cpu(), allmap=others.cpu(), radii=radii.cpu().numpy(), visible=vis,
+                depths=fb(g, go[1], 4 * P, np.float32), rect=fb(g, go[2], 8 * P, np.uint16).reshape(P, 4),
+                tiles_touched=fb(g, go[3], 4 * P, np.uint32), offsets=fb(g, go[4], 4 * P, np.uint32),
+                means2D=np.stack([rec[:, 3], rec[:, 7]], -1),
+                transMat=np.concatenate([rec[:, 0:3], rec[:, 4:7], rec[:, 8:11]], -1),
+                normal_opacity=np.concatenate([rec[:, 12:15], rec[:, 11:12]], -1),
+                keys=keys_sorted, point_list=point_list.cpu().numpy()[:R].view(np.uint32),
+                ranges=fb(im, io[0], 8 * tiles_n, np.uint32).reshape(tiles_n, 2),
+                final_T=fb(im, io[1], 12 * N, np.float32).reshape(3, N),
+                n_contrib=fb(im, io[2], 8 * N, np.uint32).reshape(2, N))
+
+
+def _higher_msb(n):
+    msb, step = 16, 16
+    while step > 1:
+        step //= 2
+        msb = msb + step if n >> msb else msb - step
+    if n >> msb:
+        msb += 1
+    return msb
+
+
+def rel_err(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).abs().sum() / b.abs().sum().clamp(min=1e-30))

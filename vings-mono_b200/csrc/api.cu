@@ -1,0 +1,164 @@
+// C ABI of the surfel rasterizer (declared in include/surfel_b200.h): stage sequencing, workspace
+// carving and error reporting.  Replaces the host drivers CudaRasterizer::Rasterizer::forward/backward
+// (DSR/cuda_rasterizer/rasterizer_impl.cu:305-478, 482-599).
+#include "common.cuh"
+#include "../../include/surfel_b200.h"
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+static thread_local char g_err[512] = "";
+
+void sb_set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+extern "C" {
+
+int sb200_abi_version(void) { return 1; }
+const char* sb200_last_error(void) { return g_err; }
+
+size_t sb200_geom_bytes(int64_t P) { return sb_geom_layout(P).total; }
+size_t sb200_image_bytes(int W, int H) { return sb_image_layout(W, H).total; }
+size_t sb200_binning_bytes(int64_t R) { return sb_bin_layout(R).total; }
+size_t sb200_grad_bytes(int64_t P) { return sb_align((size_t)(P > 0 ? P : 0) * SB_GRAD_F * 4); }
+
+void sb200_geom_layout(int64_t P, size_t out[5]) {
+    SbGeomLayout L = sb_geom_layout(P);
+    out[0] = L.rec; out[1] = L.depth; out[2] = L.rect; out[3] = L.tiles; out[4] = L.offsets;
+}
+void sb200_image_layout(int W, int H, size_t out[3]) {
+    SbImageLayout L = sb_image_layout(W, H);
+    out[0] = L.ranges; out[1] = L.final_T; out[2] = L.n_contrib;
+}
+void sb200_binning_layout(int64_t R, size_t out[4]) {
+    SbBinLayout L = sb_bin_layout(R);
+    out[0] = L.keys_a; out[1] = L.keys_b; out[2] = L.vals_a; out[3] = L.vals_b;
+}
+
+static int check_dims(int P, int W, int H) {
+    if (P < 0 || W <= 0 || H <= 0) { sb_set_error("bad dimensions P=%d W=%d H=%d", P, W, H); return 1; }
+    if ((W + SB_TILE_X - 1) / SB_TILE_X > 65535 || (H + SB_TILE_Y - 1) / SB_TILE_Y > 65535) {
+        sb_set_error("image %dx%d exceeds the 65535-tile rect encoding", W, H);
+        return 1;
+    }
+    return 0;
+}
+
+int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                        const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
+                        void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream) {
+    g_err[0] = 0;
+    if (check_dims(P, W, H)) return 1;
+    if (!num_rendered_host) { sb_set_error("num_rendered_host is NULL"); return 1; }
+    *num_rendered_host = 0;
+    if (P == 0) return 0;  // reference: rasterize_points.cu:106
+    if (!means3D || !scales || !rotations || !opacities || !colors || !viewmatrix || !projmatrix || !geom_ws || !radii) {
+        sb_set_error("forward_begin: NULL input");
+        return 1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
+                                  (char*)geom_ws, radii, s);
+    if (rc) return rc;
+    SbGeomLayout L = sb_geom_layout(P);
+    const int nblocks = (P + 255) / 256;
+    const unsigned long long* total = (const unsigned long long*)((char*)geom_ws + L.scan_state) + nblocks + 1;
+    SB_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, total, 8, cudaMemcpyDeviceToHost, s));
+    SB_CUDA_CHECK(cudaStreamSynchronize(s));
+    return 0;
+}
+
+int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* geom_ws, void* binning_ws,
+                         uint32_t* point_list, void* image_ws, float* out_color, float* out_others, void* stream) {
+    g_err[0] = 0;
+    if (check_dims(P, W, H)) return 1;
+    if (!bg || !image_ws || !out_color || !out_others) { sb_set_error("forward_finish: NULL input"); return 1; }
+    if (R > 0 && (!geom_ws || !binning_ws || !point_list)) { sb_set_error("forward_finish: NULL workspace"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    const int tiles = ((W + SB_TILE_X - 1) / SB_TILE_X) * ((H + SB_TILE_Y - 1) / SB_TILE_Y);
+    SbImageLayout IL = sb_image_layout(W, H);
+    uint64_t* keys_sorted = nullptr;
+    int rc;
+    if (R > 0) {
+        SbBinLayout BL = sb_bin_layout(R);
+        char* bw = (char*)binning_ws;
+        uint64_t* keys_a = (uint64_t*)(bw + BL.keys_a);
+        uint64_t* keys_b = (uint64_t*)(bw + BL.keys_b);
+        uint32_t* vals_a = (uint32_t*)(bw + BL.vals_a);
+        uint32_t* vals_b = (uint32_t*)(bw + BL.vals_b);
+        rc = sb_launch_duplicate(P, W, H, (const char*)geom_ws, keys_a, vals_a, s);
+        if (rc) return rc;
+        const int end_bit = 32 + (int)sb_higher_msb((uint32_t)tiles);
+        rc = sb_launch_sort_pairs(keys_a, vals_a, keys_b, vals_b, &keys_sorted, point_list, R, end_bit, bw, BL, s);
+        if (rc) return rc;
+    }
+    rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges), s);
+    if (rc) return rc;
+    // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does
+    return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others, s);
+}
+
+int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                   const float* means3D, const float* scales, const float* rotations, const float* viewmatrix,
+                   const float* projmatrix, const int* radii, const void* geom_ws, const uint32_t* point_list,
+                   const void* image_ws, const float* out_color, const float* out_others,
+                   const float* dL_dout_color, const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws,
+                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dscales,
+                   float* dL_drotations, float* dL_dtransMat, float* scores, void* stream) {
+    g_err[0] = 0;
+    if (check_dims(P, W, H)) return 1;
+    if (P == 0) return 0;  // reference: rasterize_points.cu:217
+    if (!geom_ws || !image_ws || !grad_ws || !radii || !dL_dout_color || !dL_dout_others || !pixel_mask ||
+        !dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations || !scores) {
+        sb_set_error("backward: NULL input");
+        return 1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
+    int rc;
+    if (R > 0) {
+        rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
+                                      out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
+                                      (float*)grad_ws, s);
+        if (rc) return rc;
+    }
+    return sb_launch_preprocess_backward(P, W, H, tanfovx, tanfovy, means3D, scales, rotations, viewmatrix, projmatrix,
+                                         radii, (const char*)geom_ws, (const float*)grad_ws, dL_dmeans3D, dL_dmeans2D,
+                                         dL_dcolors, dL_dopacity, dL_dscales, dL_drotations, dL_dtransMat, scores, s);
+}
+
+int sb200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                       uint8_t* present, void* stream) {
+    g_err[0] = 0;
+    (void)projmatrix;  // the reference computes p_hom from it and never uses the result (auxiliary.h:207-212)
+    if (P < 0) { sb_set_error("bad P"); return 1; }
+    return sb_launch_mark_visible(P, means3D, viewmatrix, (bool*)present, (cudaStream_t)stream);
+}
+
+int sb200_adam_update(float* param, const float* param_grad, float* exp_avg, float* exp_avg_sq,
+                      const uint8_t* visible, float lr, float b1, float b2, float eps, uint32_t N, uint32_t M,
+                      void* stream) {
+    g_err[0] = 0;
+    return sb_launch_adam(param, param_grad, exp_avg, exp_avg_sq, (const bool*)visible, lr, b1, b2, eps, N, M,
+                          (cudaStream_t)stream);
+}
+
+int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, uint64_t* keys_out, uint32_t* vals_out, void* stream) {
+    g_err[0] = 0;
+    if (n <= 0) return 0;
+    cudaStream_t s = (cudaStream_t)stream;
+    SbBinLayout BL = sb_bin_layout(n);
+    char* bw = (char*)binning_ws;
+    uint64_t* keys_sorted = nullptr;
+    int rc = sb_launch_sort_pairs((uint64_t*)(bw + BL.keys_a), (uint32_t*)(bw + BL.vals_a), (uint64_t*)(bw + BL.keys_b),
+                                  (uint32_t*)(bw + BL.vals_b), &keys_sorted, vals_out, n, end_bit, bw, BL, s);
+    if (rc) return rc;
+    SB_CUDA_CHECK(cudaMemcpyAsync(keys_out, keys_sorted, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,332 @@
+// K4a: backward of the per-tile blend.
+//
+// Restates the *live* backward of the reference, PerGaussianRenderCUDA
+// (DSR/cuda_rasterizer/backward.cu:445-845), including its quirks:
+// the gradient formulas use prefix-minus-final accumulators "ar", a transmittance re-propagated front
+// to back, M1/M2 frozen at each 32-splat bucket start, and no p.z==0 / depth<near skips.
+//
+// The reference needs 12-float-per-pixel checkpoints every 32 splats (written by its forward) so that
+// one warp per bucket can start mid-tile.  Here one CTA owns a tile and walks it front to back once,
+// recomputing the forward state on the fly, so no checkpoint is ever written or read.  A thread owns
+// a pixel; for each splat the 20 per-splat gradient terms of the 32 pixels of a warp are reduced with
+// a 21-shuffle multi-value butterfly (only when some lane of the warp actually hit the splat), the 8
+// warps' partial sums meet in shared memory, and ONE global atomic per (tile, splat, term) is issued -
+// the same count as the reference's per-bucket-lane atomics, with no 23-register shuffle pipeline.
+#include "common.cuh"
+#include <cuda_pipeline.h>
+
+#define BB_THREADS 256
+#define BB_WARPS 8
+#define BB_BATCH 32  // == the reference's bucket size; bucket boundaries are part of the semantics (Q5)
+
+// Multi-value warp reduction: every lane holds v[0..K); afterwards lane L holds in v[0] the warp-wide
+// sum of value slot(L) (or junk if slot(L) < 0).  Each step halves the number of live values.
+template <int N, int OFF>
+struct Butterfly {
+    static __device__ __forceinline__ void run(float* v, int lane) {
+        constexpr int HALF = (N + 1) / 2;
+        const bool upper = (lane & OFF) != 0;
+#pragma unroll
+        for (int i = 0; i < HALF; i++) {
+            float lo = v[i];
+            float hi = (i + HALF < N) ? v[i + HALF] : 0.f;
+            float send = upper ? lo : hi;
+            float keep = upper ? hi : lo;
+            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, OFF);
+        }
+        Butterfly<HALF, OFF / 2>::run(v, lane);
+    }
+};
+template <int N>
+struct Butterfly<N, 0> {
+    static __device__ __forceinline__ void run(float*, int) {}
+};
+
+// Which value slot ends up in this lane's v[0] (-1: none).  n_ct follows the compile-time halving
+// path of Butterfly<K,16>; n_real counts how many real (non-padding) values the lane's group holds.
+__device__ __forceinline__ int butterfly_slot(int lane, int K) {
+    int base = 0, n_ct = K, n_real = K;
+    for (int off = 16; off > 0; off >>= 1) {
+        int half = (n_ct + 1) / 2;
+        if (lane & off) {
+            base += half;
+            n_real -= half;
+        } else {
+            n_real = min(n_real, half);
+        }
+        n_ct = half;
+    }
+    return n_real >= 1 ? base : -1;
+}
+
+__global__ void __launch_bounds__(BB_THREADS)
+sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
+                         const float* __restrict__ bg, const float* __restrict__ final_T,
+                         const uint32_t* __restrict__ n_contrib, const float* __restrict__ out_color,
+                         const float* __restrict__ out_others, const float* __restrict__ dL_dpixels,
+                         const float* __restrict__ dL_dothers, const bool* __restrict__ pixel_mask,
+                         float* __restrict__ grad_acc) {
+    __shared__ __align__(16) float4 s_rec[2][BB_BATCH][SB_REC_F4];
+    __shared__ uint32_t s_id[2][BB_BATCH];
+    __shared__ float s_acc[BB_WARPS][BB_BATCH][SB_GRAD_F];
+    __shared__ uint32_t s_wmask[BB_WARPS];
+    __shared__ uint32_t s_maxlast[BB_WARPS];
+
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const uint32_t tile = blockIdx.x;
+    const uint32_t tx = tile % grid_x, ty = tile / grid_x;
+    const uint32_t px = tx * SB_TILE_X + (tid & 15), py = ty * SB_TILE_Y + (tid >> 4);
+    const bool inside = px < (uint32_t)W && py < (uint32_t)H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float2 pixf = {(float)px, (float)py};
+    const size_t HW = (size_t)H * W;
+
+    const uint2 range = ranges[tile];
+    const int n = (int)(range.y - range.x);
+
+    // per-pixel constants
+    uint32_t last = 0;
+    float T_final = 0.f, M1_final = 0.f;
+    float dLc[3] = {0.f, 0.f, 0.f}, dLn[3] = {0.f, 0.f, 0.f};
+    float dLd = 0.f, dLa = 0.f, dLreg = 0.f, fin_reg = 0.f;
+    // "ar" accumulators: prefix - final  (colour 0..2, depth 3, accum 4, normal 5..7)
+    float ar[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (inside && pixel_mask[pix_id]) {  // masked pixels contribute nothing (Q14)
+        last = n_contrib[pix_id];
+        T_final = final_T[pix_id];
+        M1_final = final_T[pix_id + HW];
+#pragma unroll
+        for (int ch = 0; ch < 3; ch++) {
+            dLc[ch] = dL_dpixels[ch * HW + pix_id];
+            ar[ch] = -out_color[ch * HW + pix_id];  // includes T_final*bg, as in the reference (Q6)
+            dLn[ch] = dL_dothers[(2 + ch) * HW + pix_id];
+            ar[5 + ch] = -out_others[(2 + ch) * HW + pix_id];
+        }
+        dLd = dL_dothers[pix_id];
+        dLa = dL_dothers[HW + pix_id];
+        dLreg = dL_dothers[6 * HW + pix_id];
+        ar[3] = -out_others[pix_id];
+        ar[4] = -out_others[HW + pix_id];
+        fin_reg = out_others[6 * HW + pix_id];
+        // median-depth channel (5) deliberately receives no gradient (Q3)
+    }
+    const float bgc[3] = {bg[0], bg[1], bg[2]};
+
+    // tile-wide max of `last` bounds the walk (reference: max_contrib bucket skip, backward.cu:503-505)
+    uint32_t wmax = last;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    if (lane == 0) s_maxlast[wid] = wmax;
+    __syncthreads();
+    uint32_t maxlast = 0;
+#pragma unroll
+    for (int w = 0; w < BB_WARPS; w++) maxlast = max(maxlast, s_maxlast[w]);
+    const int n_walk = min(n, (int)maxlast);
+    const int nbatches = (n_walk + BB_BATCH - 1) / BB_BATCH;
+    const bool warp_active = wmax > 0;
+
+    auto issue = [&](int b) {
+        const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
+        const uint32_t* ids = point_list + range.x + b * BB_BATCH;
+        if (tid < cnt * SB_REC_F4) {
+            int sp = tid / SB_REC_F4, q = tid - sp * SB_REC_F4;
+            uint32_t id = __ldg(ids + sp);
+            if (q == 0) s_id[b & 1][sp] = id;
+            __pipeline_memcpy_async(&s_rec[b & 1][sp][q], rec + (size_t)id * SB_REC_F4 + q, 16);
+        }
+        __pipeline_commit();
+    };
+
+    // running state
+    float T = 1.f;              // transmittance as the backward propagates it
+    float ar_reg = 0.f;         // distortion accumulator (reset from the true prefix at bucket starts)
+    float M1 = 0.f, M2 = 0.f;   // true forward moments (running)
+    float reg_f = 0.f;          // true forward distortion prefix
+    float M1b = 0.f, M2b = 0.f; // moments frozen at the bucket start (Q5)
+    // shadow of the true forward state, live only after a forward-skipped splat was blended by the
+    // backward inside the current bucket (Q4); the next bucket start snaps back to it
+    bool div = false;
+    float Tf = 1.f;
+    float arf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+
+    const int slot = butterfly_slot(lane, SB_GRAD_F);
+
+    if (nbatches > 0) issue(0);
+    for (int b = 0; b < nbatches; b++) {
+        if (b + 1 < nbatches) {
+            issue(b + 1);
+            __pipeline_wait_prior(1);
+        } else {
+            __pipeline_wait_prior(0);
+        }
+        __syncthreads();
+        const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
+        uint32_t cmask = 0;
+        if (warp_active) {
+            // ---- bucket start: what the reference reloads from its checkpoint ----
+            if (div) {
+                T = Tf;
+#pragma unroll
+                for (int i = 0; i < 8; i++) ar[i] = arf[i];
+                div = false;
+            }
+            ar_reg = reg_f - fin_reg;
+            M1b = M1;
+            M2b = M2;
+            const float4(*sr)[SB_REC_F4] = s_rec[b & 1];
+            for (int j = 0; j < cnt; j++) {
+                float g[SB_GRAD_F];
+#pragma unroll
+                for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
+                bool hit = false;
+                if ((uint32_t)(b * BB_BATCH + j) < last) {
+                    const float4 q0 = sr[j][0], q1 = sr[j][1], q2 = sr[j][2];
+                    const float3 Tu = {q0.x, q0.y, q0.z}, Tv = {q1.x, q1.y, q1.z}, Tw = {q2.x, q2.y, q2.z};
+                    const float2 xy = {q0.w, q1.w};
+                    const float opa = q2.w;
+                    float3 k = {pixf.x * Tw.x - Tu.x, pixf.x * Tw.y - Tu.y, pixf.x * Tw.z - Tu.z};
+                    float3 l = {pixf.y * Tw.x - Tv.x, pixf.y * Tw.y - Tv.y, pixf.y * Tw.z - Tv.z};
+                    float3 p = {k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x};
+                    float2 s = {p.x / p.z, p.y / p.z};
+                    float rho3d = (s.x * s.x + s.y * s.y);
+                    float2 d = {xy.x - pixf.x, xy.y - pixf.y};
+                    float rho2d = SB_FILTER_INV_SQUARE * (d.x * d.x + d.y * d.y);
+                    float c_d = (rho3d <= rho2d) ? (s.x * Tw.x + s.y * Tw.y) + Tw.z : Tw.z;
+                    float rho = fminf(rho3d, rho2d);
+                    float power = -0.5f * rho;
+                    if (!(power > 0.0f)) {
+                        const float G = expf(power);
+                        const float alpha = fminf(0.99f, opa * G);
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            hit = true;
+                            const float4 q3 = sr[j][3], q4 = sr[j][4];
+                            const float c[3] = {q3.w, q4.x, q4.y};
+                            const float nrm[3] = {q3.x, q3.y, q3.z};
+                            const float m_d = SB_FAR / (SB_FAR - SB_NEAR) * (1 - SB_NEAR / c_d);
+                            const float dmd_dd = (SB_FAR * SB_NEAR) / ((SB_FAR - SB_NEAR) * c_d * c_d);
+                            // would the forward have skipped this splat?  (forward.cu:408,417)
+                            const bool fwd_skip = (p.z == 0.0f) || (c_d < SB_NEAR);
+                            if (fwd_skip && !div) {
+                                div = true;
+                                Tf = T;
+#pragma unroll
+                                for (int i = 0; i < 8; i++) arf[i] = ar[i];
+                            }
+                            // ---- true forward bookkeeping (moments + distortion prefix) ----
+                            if (!fwd_skip) {
+                                const float Tt = div ? Tf : T;
+                                const float wf = alpha * Tt;
+                                reg_f += (m_d * m_d * (1 - Tt) + M2 - 2 * m_d * M1) * wf;
+                                M1 += m_d * wf;
+                                M2 += m_d * m_d * wf;
+                                if (div) {
+                                    arf[0] += wf * c[0]; arf[1] += wf * c[1]; arf[2] += wf * c[2];
+                                    arf[3] += wf * c_d;  arf[4] += wf;
+                                    arf[5] += wf * nrm[0]; arf[6] += wf * nrm[1]; arf[7] += wf * nrm[2];
+                                    Tf = Tf * (1 - alpha);
+                                }
+                            }
+                            // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
+                            const float dchannel_dcolor = alpha * T;
+                            const float inv1ma = 1.0f / (1.0f - alpha);
+                            float bg_dot_dpixel = 0.0f;
+                            float dL_dalpha = 0.0f;
+#pragma unroll
+                            for (int ch = 0; ch < 3; ch++) {
+                                ar[ch] += T * alpha * c[ch];
+                                g[15 + ch] = dchannel_dcolor * dLc[ch];
+                                dL_dalpha += ((c[ch] * T) - inv1ma * (-ar[ch])) * dLc[ch];
+                                bg_dot_dpixel += bgc[ch] * dLc[ch];
+                                g[19] += fabsf(dchannel_dcolor * dLc[ch]);
+                            }
+                            dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
+                            g[18] = dchannel_dcolor;
+                            float dL_dz = 0.0f;
+                            ar[3] += T * alpha * c_d;
+                            dL_dalpha += ((c_d * T) - inv1ma * (-ar[3])) * dLd;
+                            dL_dz += alpha * T * dLd;
+                            ar[4] += T * alpha * 1.0f;
+                            dL_dalpha += ((1.0f * T) - inv1ma * (-ar[4])) * dLa;
+#pragma unroll
+                            for (int ch = 0; ch < 3; ch++) {
+                                ar[5 + ch] += T * alpha * nrm[ch];
+                                g[11 + ch] = dchannel_dcolor * dLn[ch];
+                                dL_dalpha += ((nrm[ch] * T) - inv1ma * (-ar[5 + ch])) * dLn[ch];
+                            }
+                            const float A = 1 - T;
+                            const float dist = (m_d * m_d * A + M2b - 2 * m_d * M1b);
+                            ar_reg += T * alpha * dist;
+                            dL_dalpha += ((dist * T) - inv1ma * (-ar_reg)) * dLreg;
+                            const float final_A = 1 - T_final;
+                            const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - M1_final) * dLreg;
+                            dL_dz += dL_dmd * dmd_dd;
+                            T *= (1.0f - alpha);
+
+                            const float dL_dG = opa * dL_dalpha;
+                            if (rho3d <= rho2d) {
+                                const float2 dL_ds = {dL_dG * -G * s.x + dL_dz * Tw.x, dL_dG * -G * s.y + dL_dz * Tw.y};
+                                const float dsx_pz = dL_ds.x / p.z;
+                                const float dsy_pz = dL_ds.y / p.z;
+                                const float3 dL_dp = {dsx_pz, dsy_pz, -(dsx_pz * s.x + dsy_pz * s.y)};
+                                const float3 dL_dk = {l.y * dL_dp.z - l.z * dL_dp.y, l.z * dL_dp.x - l.x * dL_dp.z,
+                                                      l.x * dL_dp.y - l.y * dL_dp.x};
+                                const float3 dL_dl = {dL_dp.y * k.z - dL_dp.z * k.y, dL_dp.z * k.x - dL_dp.x * k.z,
+                                                      dL_dp.x * k.y - dL_dp.y * k.x};
+                                g[0] = -dL_dk.x; g[1] = -dL_dk.y; g[2] = -dL_dk.z;
+                                g[3] = -dL_dl.x; g[4] = -dL_dl.y; g[5] = -dL_dl.z;
+                                g[6] = pixf.x * dL_dk.x + pixf.y * dL_dl.x + dL_dz * s.x;
+                                g[7] = pixf.x * dL_dk.y + pixf.y * dL_dl.y + dL_dz * s.y;
+                                g[8] = pixf.x * dL_dk.z + pixf.y * dL_dl.z + dL_dz * 1.0f;
+                            } else {
+                                const float dG_ddelx = -G * SB_FILTER_INV_SQUARE * d.x;
+                                const float dG_ddely = -G * SB_FILTER_INV_SQUARE * d.y;
+                                g[9] = dL_dG * dG_ddelx;
+                                g[10] = dL_dG * dG_ddely;
+                                g[8] = dL_dz;
+                            }
+                            g[14] = G * dL_dalpha;
+                        }
+                    }
+                }
+                if (__any_sync(0xffffffffu, hit)) {
+                    Butterfly<SB_GRAD_F, 16>::run(g, lane);
+                    if (slot >= 0) s_acc[wid][j][slot] = g[0];
+                    cmask |= 1u << j;
+                }
+            }
+        }
+        if (lane == 0) s_wmask[wid] = cmask;
+        __syncthreads();
+        // ---- combine the 8 warps' partial sums; one global atomic per (splat, term) ----
+        for (int e = tid; e < cnt * SB_GRAD_F; e += BB_THREADS) {
+            int j = e / SB_GRAD_F, comp = e - j * SB_GRAD_F;
+            float sum = 0.f;
+            bool any = false;
+#pragma unroll
+            for (int w = 0; w < BB_WARPS; w++) {
+                if ((s_wmask[w] >> j) & 1u) {
+                    sum += s_acc[w][j][comp];
+                    any = true;
+                }
+            }
+            if (any) atomicAdd(grad_acc + (size_t)s_id[b & 1][j] * SB_GRAD_F + comp, sum);
+        }
+        __syncthreads();
+    }
+    __pipeline_wait_prior(0);
+}
+
+int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
+                             const char* image, const float* out_color, const float* out_others,
+                             const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
+                             float* grad_acc, cudaStream_t s) {
+    SbImageLayout IL = sb_image_layout(W, H);
+    const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
+    sb_blend_backward_kernel<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
+        W, H, grid_x, (const uint2*)(image + IL.ranges), point_list, (const float4*)geom, bg,
+        (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
+        dL_dcolor, dL_dothers, pixel_mask, grad_acc);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}

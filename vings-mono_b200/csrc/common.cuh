@@ -1,0 +1,165 @@
+// Shared definitions for the B200 surfel rasterizer kernels (sm_100a).
+//
+// Domain vocabulary follows the reference (diff-surfel-rasterization, "DSR"):
+//   surfel  = one 2D Gaussian, P of them
+//   tile    = 16x16 pixel block (DSR/cuda_rasterizer/config.h:17-18) -- part of the key contract
+//   pair    = one (tile, surfel) overlap, R = num_rendered of them
+//   record  = the packed per-surfel render record this implementation blends from
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#define SB_TILE_X 16
+#define SB_TILE_Y 16
+#define SB_TILE_PIX 256
+#define SB_NEAR 0.2f    // DSR/cuda_rasterizer/auxiliary.h:37
+#define SB_FAR 100.0f   // DSR/cuda_rasterizer/auxiliary.h:38
+#define SB_FILTER_INV_SQUARE 2.0f  // auxiliary.h:39
+
+// Per-surfel render record: 5 x float4 = 80 B, 16-B aligned, fetched as one unit by the blend kernels.
+//   q0 = (Tu.x, Tu.y, Tu.z, xy.x)
+//   q1 = (Tv.x, Tv.y, Tv.z, xy.y)
+//   q2 = (Tw.x, Tw.y, Tw.z, opacity)
+//   q3 = (n.x,  n.y,  n.z,  r)
+//   q4 = (g,    b,    depth, 0)
+#define SB_REC_F4 5
+
+// Per-surfel gradient accumulation record (floats), filled by the backward blend kernel with
+// atomics and consumed by the backward preprocess kernel.
+//   0..8  dL/dT (Tu, Tv, Tw)   9..10 dL/dmean2D (low-pass branch)   11..13 dL/dnormal
+//   14    dL/dopacity          15..17 dL/dcolor                     18..19 scores
+#define SB_GRAD_F 20
+
+static inline __host__ __device__ size_t sb_align(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
+
+// Geometry workspace (caller-allocated, P-sized). Offsets in bytes.
+struct SbGeomLayout {
+    size_t rec;        // float4[5P]
+    size_t depth;      // float[P]       view-space z (key low word)
+    size_t rect;       // ushort4[P]     tile rect (min.x, min.y, max.x, max.y)
+    size_t tiles;      // uint32[P]      tiles_touched
+    size_t offsets;    // uint32[P]      inclusive prefix sum of tiles_touched
+    size_t scan_state; // uint64[nblk+2] look-back status words + ticket + total
+    size_t total;
+};
+
+static inline __host__ SbGeomLayout sb_geom_layout(int64_t P) {
+    SbGeomLayout L;
+    size_t o = 0;
+    size_t p = (size_t)(P > 0 ? P : 0);
+    L.rec = o;        o = sb_align(o + p * SB_REC_F4 * 16);
+    L.depth = o;      o = sb_align(o + p * 4);
+    L.rect = o;       o = sb_align(o + p * 8);
+    L.tiles = o;      o = sb_align(o + p * 4);
+    L.offsets = o;    o = sb_align(o + p * 4);
+    L.scan_state = o; o = sb_align(o + ((p + 255) / 256 + 4) * 8);
+    L.total = o;
+    return L;
+}
+
+// Image workspace (caller-allocated): tile ranges + the per-pixel state the backward needs.
+struct SbImageLayout {
+    size_t ranges;    // uint2[tiles]
+    size_t final_T;   // float[3*HW]   T, M1, M2   (reference: ImageState::accum_alpha)
+    size_t n_contrib; // uint32[2*HW]  last contributor, median contributor
+    size_t total;
+};
+
+static inline __host__ SbImageLayout sb_image_layout(int W, int H) {
+    SbImageLayout L;
+    size_t tiles = (size_t)((W + SB_TILE_X - 1) / SB_TILE_X) * ((H + SB_TILE_Y - 1) / SB_TILE_Y);
+    size_t hw = (size_t)W * H;
+    size_t o = 0;
+    L.ranges = o;    o = sb_align(o + tiles * 8);
+    L.final_T = o;   o = sb_align(o + hw * 12);
+    L.n_contrib = o; o = sb_align(o + hw * 8);
+    L.total = o;
+    return L;
+}
+
+// Radix sort geometry (onesweep).
+#define SB_SORT_THREADS 256
+#define SB_SORT_ITEMS 16
+#define SB_SORT_TILE (SB_SORT_THREADS * SB_SORT_ITEMS)
+#define SB_RADIX_BITS 8
+#define SB_RADIX 256
+#define SB_MAX_PASSES 8
+
+// Binning scratch (caller-allocated, R-sized; only point_list survives the forward and it is a
+// separate caller buffer).
+struct SbBinLayout {
+    size_t keys_a, keys_b;  // uint64[R]
+    size_t vals_a, vals_b;  // uint32[R]
+    size_t hist;            // uint32[SB_MAX_PASSES*256] global digit histograms -> exclusive bases
+    size_t tickets;         // uint32[SB_MAX_PASSES]
+    size_t status;          // uint32[passes * ntiles * 256] look-back words
+    size_t zero_begin, zero_bytes; // the region that must be zeroed before a sort
+    size_t total;
+};
+
+static inline __host__ SbBinLayout sb_bin_layout(int64_t R) {
+    SbBinLayout L;
+    size_t r = (size_t)(R > 0 ? R : 0);
+    size_t ntiles = (r + SB_SORT_TILE - 1) / SB_SORT_TILE;
+    size_t o = 0;
+    L.keys_a = o; o = sb_align(o + r * 8);
+    L.keys_b = o; o = sb_align(o + r * 8);
+    L.vals_a = o; o = sb_align(o + r * 4);
+    L.vals_b = o; o = sb_align(o + r * 4);
+    L.zero_begin = o;
+    L.hist = o;    o = sb_align(o + SB_MAX_PASSES * SB_RADIX * 4);
+    L.tickets = o; o = sb_align(o + SB_MAX_PASSES * 4);
+    L.status = o;  o = sb_align(o + (size_t)SB_MAX_PASSES * ntiles * SB_RADIX * 4);
+    L.zero_bytes = o - L.zero_begin;
+    L.total = o;
+    return L;
+}
+
+// Same bit count the reference passes to its sort: 32 + getHigherMsb(tiles)
+// (DSR/cuda_rasterizer/rasterizer_impl.cu:35-50,410).
+static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
+    uint32_t msb = sizeof(n) * 4;
+    uint32_t step = msb;
+    while (step > 1) {
+        step /= 2;
+        if (n >> msb) msb += step; else msb -= step;
+    }
+    if (n >> msb) msb++;
+    return msb;
+}
+
+void sb_set_error(const char* fmt, ...);
+#define SB_CUDA_CHECK(expr)                                                              \
+    do {                                                                                 \
+        cudaError_t _e = (expr);                                                         \
+        if (_e != cudaSuccess) {                                                         \
+            sb_set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return 2;                                                                    \
+        }                                                                                \
+    } while (0)
+
+// Stage launchers (defined in the .cu files, sequenced by api.cu).
+int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                         const float* opacities, const float* colors, const float* viewmatrix,
+                         const float* projmatrix, char* geom, int* radii, cudaStream_t s);
+int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
+int sb_launch_duplicate(int P, int W, int H, const char* geom, uint64_t* keys, uint32_t* vals, cudaStream_t s);
+int sb_launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_tmp, uint32_t* vals_tmp,
+                         uint64_t** keys_sorted, uint32_t* vals_final, int64_t n, int end_bit, char* bin_base,
+                         const SbBinLayout& L, cudaStream_t s);
+int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, cudaStream_t s);
+int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
+                            char* image, float* out_color, float* out_others, cudaStream_t s);
+int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
+                             const char* image, const float* out_color, const float* out_others,
+                             const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
+                             float* grad_acc, cudaStream_t s);
+int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanfovy, const float* means3D,
+                                  const float* scales, const float* rotations, const float* viewmatrix,
+                                  const float* projmatrix, const int* radii, const char* geom, const float* grad_acc,
+                                  float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
+                                  float* dL_dscales, float* dL_drotations, float* dL_dtransMat, float* scores,
+                                  cudaStream_t s);
+int sb_launch_adam(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, const bool* visible,
+                   float lr, float b1, float b2, float eps, uint32_t N, uint32_t M, cudaStream_t s);

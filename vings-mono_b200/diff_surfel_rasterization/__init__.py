@@ -1,0 +1,316 @@
+"""B200-native drop-in for VINGS-Mono's ``diff_surfel_rasterization`` module.
+
+Same public names and call contract as the reference wrapper
+(submodules/diff-surfel-rasterization/diff_surfel_rasterization/__init__.py):
+
+* ``GaussianRasterizationSettings``  (:171-184)  -- 13 required fields, no defaults
+* ``GaussianRasterizer``             (:186-237)  -- ``forward(...) -> (color, radii, allmap)``, ``markVisible``
+* ``SparseGaussianAdam``             (:241-268)  -- visibility-masked Adam, ``step(visibility, N)``
+* ``rasterize_gaussians`` / ``_RasterizeGaussians`` (:21-169) -- autograd contract; ``scores`` is delivered
+  through the gradient slot of the ``scores`` input.
+
+PyTorch is plumbing only (device memory, streams, autograd graph).  All compute is hand-written
+sm_100a CUDA in ``libsurfel_b200.so`` reached through the C ABI of ``include/surfel_b200.h`` with
+ctypes.  There is no CPU path and no fallback: importing works without a GPU (so host logic can be
+tested), but any compute call without the library or without CUDA tensors raises.
+"""
+import ctypes
+import os
+from typing import NamedTuple
+
+import torch
+import torch.nn as nn
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libsurfel_b200.so")
+_lib = None
+
+_vp = ctypes.c_void_p
+_i32 = ctypes.c_int
+_i64 = ctypes.c_int64
+_f32 = ctypes.c_float
+_u32 = ctypes.c_uint32
+_sz = ctypes.c_size_t
+
+
+def _load():
+    """Load the C-ABI library once and declare every prototype of include/surfel_b200.h."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise RuntimeError(
+            "libsurfel_b200.so is missing (%s): build it with `python vings-mono_b200/build.py`; "
+            "there is no CPU fallback" % _LIB_PATH)
+    lib = ctypes.CDLL(_LIB_PATH)
+    lib.sb200_abi_version.restype = _i32
+    lib.sb200_last_error.restype = ctypes.c_char_p
+    for name in ("sb200_geom_bytes", "sb200_binning_bytes", "sb200_grad_bytes"):
+        getattr(lib, name).restype = _sz
+        getattr(lib, name).argtypes = [_i64]
+    lib.sb200_image_bytes.restype = _sz
+    lib.sb200_image_bytes.argtypes = [_i32, _i32]
+    lib.sb200_geom_layout.argtypes = [_i64, ctypes.POINTER(_sz)]
+    lib.sb200_geom_layout.restype = None
+    lib.sb200_image_layout.argtypes = [_i32, _i32, ctypes.POINTER(_sz)]
+    lib.sb200_image_layout.restype = None
+    lib.sb200_binning_layout.argtypes = [_i64, ctypes.POINTER(_sz)]
+    lib.sb200_binning_layout.restype = None
+    lib.sb200_forward_begin.restype = _i32
+    lib.sb200_forward_begin.argtypes = [_i32, _i32, _i32] + [_vp] * 7 + [_vp, _vp, _vp, _vp]
+    lib.sb200_forward_finish.restype = _i32
+    lib.sb200_forward_finish.argtypes = [_i32, _i32, _i32, _i64] + [_vp] * 8
+    lib.sb200_backward.restype = _i32
+    lib.sb200_backward.argtypes = [_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 24
+    lib.sb200_mark_visible.restype = _i32
+    lib.sb200_mark_visible.argtypes = [_i32, _vp, _vp, _vp, _vp, _vp]
+    lib.sb200_adam_update.restype = _i32
+    lib.sb200_adam_update.argtypes = [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _u32, _u32, _vp]
+    lib.sb200_sort_pairs.restype = _i32
+    lib.sb200_sort_pairs.argtypes = [_vp, _i64, _i32, _vp, _vp, _vp]
+    if lib.sb200_abi_version() != 1:
+        raise RuntimeError("libsurfel_b200.so ABI mismatch")
+    _lib = lib
+    return lib
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError("%s failed: %s" % (what, _load().sb200_last_error().decode()))
+
+
+def _ptr(t):
+    return _vp(t.data_ptr()) if t is not None and t.numel() > 0 else _vp(None)
+
+
+def _stream(device):
+    return _vp(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _f32c(t, name):
+    """The reference only asserts is_cuda (rasterize_points.cu:28-30) and calls .contiguous()."""
+    if not t.is_cuda:
+        raise RuntimeError("%s must be a CUDA tensor" % name)
+    if t.dtype != torch.float32:
+        raise RuntimeError("%s must be float32" % name)
+    return t.contiguous()
+
+
+# pinned 8-byte landing pad for the pair count, one per device
+_pinned_counts = {}
+
+
+def _count_buffer(device):
+    key = device.index
+    buf = _pinned_counts.get(key)
+    if buf is None:
+        buf = torch.zeros(1, dtype=torch.int64).pin_memory()
+        _pinned_counts[key] = buf
+    return buf
+
+
+class _RasterizeGaussians(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, scores, cov3Ds_precomp,
+                raster_settings):
+        lib = _load()
+        rs = raster_settings
+        if means3D.ndim != 2 or means3D.size(1) != 3:
+            raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:63-65
+        if sh is not None and sh.numel() != 0:
+            raise NotImplementedError("SH colours are not on VINGS-Mono's path (sh_degree=0, colors_precomp); Q16")
+        if cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0:
+            raise NotImplementedError("transMat_precomp is not on VINGS-Mono's path; Q16")
+        P = means3D.size(0)
+        H, W = int(rs.image_height), int(rs.image_width)
+        dev = means3D.device
+        ctx.in_shapes = [tuple(t.shape) if isinstance(t, torch.Tensor) else None
+                         for t in (means3D, means2D, sh, colors_precomp, opacities, scales, rotations, scores,
+                                   cov3Ds_precomp)] + [None]
+        means3D = _f32c(means3D, "means3D")
+        colors = _f32c(colors_precomp, "colors_precomp")
+        opac = _f32c(opacities, "opacities")
+        scales_c = _f32c(scales, "scales")
+        rot_c = _f32c(rotations, "rotations")
+        bg = _f32c(rs.bg, "bg")
+        view = _f32c(rs.viewmatrix, "viewmatrix")
+        proj = _f32c(rs.projmatrix, "projmatrix")
+
+        color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        others = torch.empty((7, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        if P == 0:  # rasterize_points.cu:106 -- outputs stay zero, nothing is rendered
+            color.zero_()
+            others.zero_()
+            ctx.empty = True
+            ctx.raster_settings = rs
+            ctx.P = 0
+            return color, radii, others
+
+        stream = _stream(dev)
+        geom = torch.empty(lib.sb200_geom_bytes(P), dtype=torch.uint8, device=dev)
+        image = torch.empty(lib.sb200_image_bytes(W, H), dtype=torch.uint8, device=dev)
+        count = _count_buffer(dev)
+        _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac), _ptr(colors),
+                                       _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii), _vp(count.data_ptr()),
+                                       stream), "sb200_forward_begin")
+        R = int(count[0])
+        # sort scratch is dead after the forward; only the sorted id list is kept for the backward
+        binning = torch.empty(lib.sb200_binning_bytes(R), dtype=torch.uint8, device=dev)
+        point_list = torch.empty((R,), dtype=torch.int32, device=dev)
+        _check(lib.sb200_forward_finish(P, W, H, R, _ptr(bg), _ptr(geom), _ptr(binning), _ptr(point_list),
+                                        _ptr(image), _ptr(color), _ptr(others), stream), "sb200_forward_finish")
+        ctx.empty = False
+        ctx.raster_settings = rs
+        ctx.P = P
+        ctx.num_rendered = R
+        ctx.save_for_backward(means3D, scales_c, rot_c, radii, geom, point_list, image, color, others)
+        ctx.mark_non_differentiable(radii)
+        return color, radii, others
+
+    @staticmethod
+    def backward(ctx, grad_out_color, grad_radii, grad_depth):
+        lib = _load()
+        rs = ctx.raster_settings
+        P = ctx.P
+        H, W = int(rs.image_height), int(rs.image_width)
+        if ctx.empty:
+            dev = grad_out_color.device
+            return tuple(torch.zeros(sh_, dtype=torch.float32, device=dev)
+                         if sh_ is not None and ctx.needs_input_grad[i] else None
+                         for i, sh_ in enumerate(ctx.in_shapes))
+        means3D, scales_c, rot_c, radii, geom, point_list, image, color, others = ctx.saved_tensors
+        dev = means3D.device
+        g_color = _f32c(grad_out_color, "grad_out_color")
+        g_others = _f32c(grad_depth, "grad_allmap")
+        mask = rs.pixel_mask
+        if not mask.is_cuda:
+            raise RuntimeError("pixel_mask must be a CUDA tensor")
+        mask = mask.contiguous()
+        if mask.dtype != torch.bool:
+            mask = mask != 0
+        if mask.numel() != H * W:
+            raise RuntimeError("pixel_mask must have H*W elements")
+        bg = rs.bg.contiguous()
+        view = rs.viewmatrix.contiguous()
+        proj = rs.projmatrix.contiguous()
+        e = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        dmeans3D, dmeans2D, dcolors, dopac = e(P, 3), e(P, 3), e(P, 3), e(P, 1)
+        dscales, drot, dtrans, scores = e(P, 2), e(P, 4), e(P, 9), e(P, 2)
+        grad_ws = torch.empty(lib.sb200_grad_bytes(P), dtype=torch.uint8, device=dev)
+        _check(lib.sb200_backward(P, W, H, ctx.num_rendered, _ptr(bg), float(rs.tanfovx), float(rs.tanfovy),
+                                  _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(view), _ptr(proj), _ptr(radii),
+                                  _ptr(geom), _ptr(point_list), _ptr(image), _ptr(color), _ptr(others),
+                                  _ptr(g_color), _ptr(g_others), _ptr(mask), _ptr(grad_ws),
+                                  _ptr(dmeans3D), _ptr(dmeans2D), _ptr(dcolors), _ptr(dopac), _ptr(dscales),
+                                  _ptr(drot), _ptr(dtrans), _ptr(scores), _stream(dev)), "sb200_backward")
+        # forward-argument order of the reference (__init__.py:156-167).  The reference hands a tensor to
+        # every slot; autograd rejects that for inputs that were None, so those slots get None here.
+        grads = [dmeans3D, dmeans2D, None, dcolors, dopac, dscales, drot, scores, None, None]
+        for i, shape in enumerate(ctx.in_shapes):
+            if shape is None or not ctx.needs_input_grad[i]:
+                grads[i] = None
+            elif grads[i] is not None and tuple(grads[i].shape) != shape:
+                grads[i] = grads[i].reshape(shape)
+        return tuple(grads)
+
+
+def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, scores, cov3Ds_precomp,
+                        raster_settings):
+    return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, scores,
+                                     cov3Ds_precomp, raster_settings)
+
+
+class GaussianRasterizationSettings(NamedTuple):
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float  # accepted and never used, like the reference (forward.cu:96)
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    pixel_mask: torch.Tensor
+
+
+class GaussianRasterizer(nn.Module):
+    def __init__(self, raster_settings):
+        super().__init__()
+        self.raster_settings = raster_settings
+
+    def markVisible(self, positions):
+        """bool[P]: view-space z > 0.2 (rasterizer_impl.cu:106-118, auxiliary.h:212)."""
+        lib = _load()
+        with torch.no_grad():
+            rs = self.raster_settings
+            pos = _f32c(positions, "positions")
+            P = pos.size(0)
+            present = torch.zeros((P,), dtype=torch.bool, device=pos.device)
+            _check(lib.sb200_mark_visible(P, _ptr(pos), _ptr(rs.viewmatrix.contiguous()),
+                                          _ptr(rs.projmatrix.contiguous()), _ptr(present), _stream(pos.device)),
+                   "sb200_mark_visible")
+        return present
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
+                cov3D_precomp=None, scores=None):
+        raster_settings = self.raster_settings
+        if (shs is None and colors_precomp is None) or (shs is not None and colors_precomp is not None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        if ((scales is None or rotations is None) and cov3D_precomp is None) or \
+                ((scales is not None or rotations is not None) and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        dev = means3D.device
+        empty = lambda: torch.empty(0, dtype=torch.float32, device=dev)
+        if shs is None:
+            shs = empty()
+        if colors_precomp is None:
+            colors_precomp = empty()
+        if scales is None:
+            scales = empty()
+        if rotations is None:
+            rotations = empty()
+        if cov3D_precomp is None:
+            cov3D_precomp = empty()
+        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations, scores,
+                                   cov3D_precomp, raster_settings)
+
+
+class SparseGaussianAdam(torch.optim.Adam):
+    """Visibility-masked Adam without bias correction (reference __init__.py:241-268, adam.cu:9-38)."""
+
+    def __init__(self, params, lr, eps):
+        super().__init__(params=params, lr=lr, eps=eps)
+
+    @torch.no_grad()
+    def step(self, visibility, N):
+        lib = _load()
+        for group in self.param_groups:
+            lr = group["lr"]
+            eps = group["eps"]
+            assert len(group["params"]) == 1, "more than one tensor in group"
+            param = group["params"][0]
+            if param.grad is None:
+                continue
+            state = self.state[param]
+            if len(state) == 0:
+                state['step'] = torch.tensor(0.0, dtype=torch.float32)
+                state['exp_avg'] = torch.zeros_like(param, memory_format=torch.preserve_format)
+                state['exp_avg_sq'] = torch.zeros_like(param, memory_format=torch.preserve_format)
+            exp_avg = state["exp_avg"]
+            exp_avg_sq = state["exp_avg_sq"]
+            M = param.numel() // N
+            if not (param.is_cuda and param.is_contiguous() and param.grad.is_contiguous()):
+                raise RuntimeError("SparseGaussianAdam needs contiguous CUDA parameters")
+            vis = visibility.contiguous()
+            if vis.dtype != torch.bool:
+                vis = vis != 0
+            _check(lib.sb200_adam_update(_ptr(param), _ptr(param.grad), _ptr(exp_avg), _ptr(exp_avg_sq), _ptr(vis),
+                                         float(lr), 0.9, 0.999, float(eps), int(N), int(M), _stream(param.device)),
+                   "sb200_adam_update")
+
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "SparseGaussianAdam", "rasterize_gaussians"]
