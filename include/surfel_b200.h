@@ -38,6 +38,26 @@ int sb200_abi_version(void);
 /* Message of the last failing call on this thread ("" if none). */
 const char* sb200_last_error(void);
 
+/* ---- measurement hooks (bench.py) ------------------------------------------------------------
+ * Number of kernels this library has launched since load (the `gpu_launches` claim of bench.py). */
+long long sb200_launch_count(void);
+/* Per-stage device timing: while enabled, every stage is bracketed by a cudaEvent pair recorded on the
+ * stream the stage is launched on.  sb200_profile_read waits for the recorded events, returns the summed
+ * milliseconds and the number of timed launches per stage since the previous read, and resets. */
+enum {
+    SB200_STAGE_PREPROCESS = 0,     /* per-surfel preprocess + tile-count prefix sum */
+    SB200_STAGE_DUPLICATE = 1,      /* tile-key duplication */
+    SB200_STAGE_SORT = 2,           /* onesweep radix sort (histogram + passes) */
+    SB200_STAGE_RANGES = 3,         /* tile ranges */
+    SB200_STAGE_BLEND_FWD = 4,      /* per-tile forward blend */
+    SB200_STAGE_BLEND_BWD = 5,      /* per-tile backward blend (+ zeroing of its accumulation record) */
+    SB200_STAGE_PREPROCESS_BWD = 6, /* per-surfel backward preprocess */
+    SB200_STAGE_ADAM = 7,           /* masked Adam update */
+    SB200_NUM_STAGES = 8
+};
+int sb200_profile_enable(int on);
+int sb200_profile_read(double ms[SB200_NUM_STAGES], long long count[SB200_NUM_STAGES]);
+
 /* ---- workspace sizes ------------------------------------------------------------------------ */
 /* per-surfel workspace (reference: GeometryState, rasterizer_impl.h:29-44); must persist forward->backward */
 size_t sb200_geom_bytes(int64_t P);

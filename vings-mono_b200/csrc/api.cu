@@ -7,7 +7,46 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
+#include <mutex>
+#include <vector>
+
 static thread_local char g_err[512] = "";
+
+// ---- optional per-stage device timing (CUDA events on the launching stream) and launch counting ----
+static std::atomic<long long> g_launches{0};
+void sb_count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+struct StageRec { int stage; cudaEvent_t e0, e1; };
+static std::mutex g_prof_mu;
+static bool g_prof_on = false;
+static std::vector<StageRec> g_prof_recs;
+static std::vector<cudaEvent_t> g_prof_pool;
+
+static cudaEvent_t prof_event() {
+    cudaEvent_t e;
+    if (!g_prof_pool.empty()) { e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct StageScope {
+    bool on; int stage; cudaStream_t s; cudaEvent_t e0;
+    StageScope(int stage_, cudaStream_t s_) : on(false), stage(stage_), s(s_), e0(nullptr) {
+        std::lock_guard<std::mutex> g(g_prof_mu);
+        if (!g_prof_on) return;
+        on = true;
+        e0 = prof_event();
+        cudaEventRecord(e0, s);
+    }
+    ~StageScope() {
+        if (!on) return;
+        std::lock_guard<std::mutex> g(g_prof_mu);
+        cudaEvent_t e1 = prof_event();
+        cudaEventRecord(e1, s);
+        g_prof_recs.push_back({stage, e0, e1});
+    }
+};
 
 void sb_set_error(const char* fmt, ...) {
     va_list ap;
@@ -18,7 +57,32 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 1; }
+int sb200_abi_version(void) { return 2; }
+
+long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int sb200_profile_enable(int on) {
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    g_prof_on = on != 0;
+    return 0;
+}
+
+int sb200_profile_read(double* ms, long long* count) {
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    for (int i = 0; i < SB200_NUM_STAGES; i++) { ms[i] = 0.0; count[i] = 0; }
+    for (StageRec& r : g_prof_recs) {
+        float t = 0.f;
+        cudaError_t e = cudaEventSynchronize(r.e1);
+        if (e == cudaSuccess) e = cudaEventElapsedTime(&t, r.e0, r.e1);
+        if (e != cudaSuccess) { sb_set_error("profile_read: %s", cudaGetErrorString(e)); return 2; }
+        ms[r.stage] += (double)t;
+        count[r.stage] += 1;
+        g_prof_pool.push_back(r.e0);
+        g_prof_pool.push_back(r.e1);
+    }
+    g_prof_recs.clear();
+    return 0;
+}
 const char* sb200_last_error(void) { return g_err; }
 
 size_t sb200_geom_bytes(int64_t P) { return sb_geom_layout(P).total; }
@@ -61,8 +125,12 @@ int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* 
         return 1;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    int rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
+    int rc;
+    {
+        StageScope sc(SB200_STAGE_PREPROCESS, s);
+        rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
                                   (char*)geom_ws, radii, s);
+    }
     if (rc) return rc;
     SbGeomLayout L = sb_geom_layout(P);
     const int nblocks = (P + 255) / 256;
@@ -90,15 +158,25 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
         uint64_t* keys_b = (uint64_t*)(bw + BL.keys_b);
         uint32_t* vals_a = (uint32_t*)(bw + BL.vals_a);
         uint32_t* vals_b = (uint32_t*)(bw + BL.vals_b);
-        rc = sb_launch_duplicate(P, W, H, (const char*)geom_ws, keys_a, vals_a, s);
+        {
+            StageScope sc(SB200_STAGE_DUPLICATE, s);
+            rc = sb_launch_duplicate(P, W, H, (const char*)geom_ws, keys_a, vals_a, s);
+        }
         if (rc) return rc;
         const int end_bit = 32 + (int)sb_higher_msb((uint32_t)tiles);
-        rc = sb_launch_sort_pairs(keys_a, vals_a, keys_b, vals_b, &keys_sorted, point_list, R, end_bit, bw, BL, s);
+        {
+            StageScope sc(SB200_STAGE_SORT, s);
+            rc = sb_launch_sort_pairs(keys_a, vals_a, keys_b, vals_b, &keys_sorted, point_list, R, end_bit, bw, BL, s);
+        }
         if (rc) return rc;
     }
-    rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges), s);
+    {
+        StageScope sc(SB200_STAGE_RANGES, s);
+        rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges), s);
+    }
     if (rc) return rc;
     // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does
+    StageScope sc(SB200_STAGE_BLEND_FWD, s);
     return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others, s);
 }
 
@@ -118,14 +196,18 @@ int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfov
         return 1;
     }
     cudaStream_t s = (cudaStream_t)stream;
-    SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
     int rc;
     if (R > 0) {
+        StageScope sc(SB200_STAGE_BLEND_BWD, s);
+        SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
         rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
                                       out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
                                       (float*)grad_ws, s);
         if (rc) return rc;
+    } else {
+        SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
     }
+    StageScope sc(SB200_STAGE_PREPROCESS_BWD, s);
     return sb_launch_preprocess_backward(P, W, H, tanfovx, tanfovy, means3D, scales, rotations, viewmatrix, projmatrix,
                                          radii, (const char*)geom_ws, (const float*)grad_ws, dL_dmeans3D, dL_dmeans2D,
                                          dL_dcolors, dL_dopacity, dL_dscales, dL_drotations, dL_dtransMat, scores, s);
@@ -143,6 +225,7 @@ int sb200_adam_update(float* param, const float* param_grad, float* exp_avg, flo
                       const uint8_t* visible, float lr, float b1, float b2, float eps, uint32_t N, uint32_t M,
                       void* stream) {
     g_err[0] = 0;
+    StageScope sc(SB200_STAGE_ADAM, (cudaStream_t)stream);
     return sb_launch_adam(param, param_grad, exp_avg, exp_avg_sq, (const bool*)visible, lr, b1, b2, eps, N, M,
                           (cudaStream_t)stream);
 }

@@ -90,6 +90,7 @@ int sb_launch_duplicate(int P, int W, int H, const char* geom, uint64_t* keys, u
                                                         (const ushort4*)(geom + L.rect),
                                                         (const uint32_t*)(geom + L.tiles),
                                                         (const uint32_t*)(geom + L.offsets), keys, vals);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
@@ -99,6 +100,7 @@ int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uin
     if (R == 0) return 0;
     int64_t nblocks = (R + 255) / 256;
     sb_tile_ranges_kernel<<<(unsigned)nblocks, 256, 0, s>>>(R, keys_sorted, ranges);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -327,6 +327,7 @@ int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, co
         W, H, grid_x, (const uint2*)(image + IL.ranges), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
         dL_dcolor, dL_dothers, pixel_mask, grad_acc);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -152,6 +152,7 @@ int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, con
     sb_blend_forward_kernel<<<grid_x * grid_y, FB_THREADS, 0, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), point_list, (const float4*)geom, bg,
         (float*)(image + IL.final_T), (uint32_t*)(image + IL.n_contrib), out_color, out_others);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

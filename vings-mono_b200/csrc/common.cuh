@@ -130,6 +130,7 @@ static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
 }
 
 void sb_set_error(const char* fmt, ...);
+void sb_count_launch(int n);  // kernels launched (reported as gpu_launches by bench.py)
 #define SB_CUDA_CHECK(expr)                                                              \
     do {                                                                                 \
         cudaError_t _e = (expr);                                                         \

@@ -177,6 +177,7 @@ int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float*
         P, W, H, means3D, (const float2*)scales, (const float4*)rotations, opacities, colors, viewmatrix, projmatrix,
         (float4*)(geom + L.rec), (float*)(geom + L.depth), (ushort4*)(geom + L.rect), (uint32_t*)(geom + L.tiles),
         (uint32_t*)(geom + L.offsets), (unsigned long long*)(geom + L.scan_state), radii, nblocks);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
@@ -184,6 +185,7 @@ int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float*
 int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s) {
     if (P == 0) return 0;
     sb_mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, viewmatrix, present);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

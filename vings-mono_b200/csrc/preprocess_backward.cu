@@ -189,6 +189,7 @@ int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanf
         P, Wq, Hq, means3D, (const float2*)scales, (const float4*)rotations, viewmatrix, projmatrix, radii,
         (const float4*)geom, grad_acc, dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity, (float2*)dL_dscales,
         (float4*)dL_drotations, dL_dtransMat, (float2*)scores);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
@@ -198,6 +199,7 @@ int sb_launch_adam(float* param, const float* grad, float* exp_avg, float* exp_a
     const uint32_t cnt = N * M;
     if (cnt == 0) return 0;
     sb_adam_kernel<<<(cnt + 255) / 256, 256, 0, s>>>(param, grad, exp_avg, exp_avg_sq, visible, lr, b1, b2, eps, N, M);
+    sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -220,6 +220,7 @@ int sb_launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint6
         kin = kout;
         vin = vout;
     }
+    sb_count_launch(2 + passes);
     SB_CUDA_CHECK(cudaGetLastError());
     *keys_sorted = const_cast<uint64_t*>(kin);
     return 0;

@@ -68,7 +68,12 @@ def _load():
     lib.sb200_adam_update.argtypes = [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _u32, _u32, _vp]
     lib.sb200_sort_pairs.restype = _i32
     lib.sb200_sort_pairs.argtypes = [_vp, _i64, _i32, _vp, _vp, _vp]
-    if lib.sb200_abi_version() != 1:
+    lib.sb200_launch_count.restype = ctypes.c_longlong
+    lib.sb200_profile_enable.restype = _i32
+    lib.sb200_profile_enable.argtypes = [_i32]
+    lib.sb200_profile_read.restype = _i32
+    lib.sb200_profile_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong)]
+    if lib.sb200_abi_version() != 2:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -107,6 +112,30 @@ def _count_buffer(device):
         buf = torch.zeros(1, dtype=torch.int64).pin_memory()
         _pinned_counts[key] = buf
     return buf
+
+
+STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam")
+
+
+def profile_enable(on=True):
+    """Bracket every stage with CUDA events on its launching stream (include/surfel_b200.h)."""
+    _check(_load().sb200_profile_enable(1 if on else 0), "sb200_profile_enable")
+
+
+def profile_read():
+    """{stage: (total_ms, launches)} since the previous read; waits for the recorded events."""
+    ms = (ctypes.c_double * len(STAGES))()
+    cnt = (ctypes.c_longlong * len(STAGES))()
+    _check(_load().sb200_profile_read(ms, cnt), "sb200_profile_read")
+    return {name: (ms[i], cnt[i]) for i, name in enumerate(STAGES)}
+
+
+def launch_count():
+    return int(_load().sb200_launch_count())
+
+
+# counters of the most recent forward on this process: P, R (tile-surfel pairs); V is (radii > 0).sum()
+last_counters = {}
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -155,6 +184,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                                        _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii), _vp(count.data_ptr()),
                                        stream), "sb200_forward_begin")
         R = int(count[0])
+        last_counters.update(P=P, R=R, W=W, H=H)
         # sort scratch is dead after the forward; only the sorted id list is kept for the backward
         binning = torch.empty(lib.sb200_binning_bytes(R), dtype=torch.uint8, device=dev)
         point_list = torch.empty((R,), dtype=torch.int32, device=dev)

@@ -1,0 +1,222 @@
+"""Host-side mapping step around the rasterizer -- the caller the drop-in sits behind.
+
+Mirrors one iteration of VINGS-Mono's ``train_once_gaussian`` loop
+(scripts/gaussian/gaussian_base.py:343-404) with the rasterizer module as a parameter, so the very
+same step can be driven through this package *or* through the unmodified reference build:
+
+    render_raw      gaussian_base.py:142-224   activations, settings, rasterizer call, depth/alpha, normals
+    get_loss        loss_utils.py:110-153      0.8 L1 + 0.2 (1-SSIM), normal, alpha, 1/cov-weighted depth, dist
+    add_records     gaussian_model.py:163-168  score bookkeeping
+    weighting_grad  gaussian_utils.py:56-62    per-surfel gradient re-weighting by importance scores
+    optimizer.step  gaussian_base.py:400-403   SparseGaussianAdam.step(radii > 0, P)
+
+Multi-GPU (new; the reference has no multi-GPU code): the views of the keyframe
+window are partitioned over the ranks, surfels are replicated, and one NCCL all-reduce of a fused
+``[P,16]`` fp32 buffer (13 parameter-gradient columns + 2 score columns + 1 visibility column)
+precedes the identical Adam step on every rank.
+
+PyTorch here is plumbing (parameters, autograd graph, loss glue); every rasterizer stage and the Adam
+update run in the module handed in.
+"""
+import math
+
+import torch
+import torch.nn.functional as F
+
+LOSS_WEIGHTS = {
+    # configs/*.yaml training_args.loss_weights; C3 adds normal + distortion supervision (BASELINE.json)
+    "rgb+depth": dict(rgb_loss=1.0, depth_loss=1.0, alpha_loss=0.5, normal_loss=0.0, dist_loss=0.0),
+    "rgb+depth+normal+dist": dict(rgb_loss=1.0, depth_loss=1.0, alpha_loss=0.5, normal_loss=0.05, dist_loss=100.0),
+    "rgb": dict(rgb_loss=1.0, depth_loss=0.0, alpha_loss=0.5, normal_loss=0.0, dist_loss=0.0),
+}
+LR = dict(_xyz=0.00002, _rgb=0.0001, _opacity=0.02, _scaling=0.001, _rotation=0.001)  # configs/rtg/hotel.yaml:70-75
+GROUPS = ("_xyz", "_rgb", "_opacity", "_scaling", "_rotation")
+GROUP_COLS = dict(_xyz=3, _rgb=3, _opacity=1, _scaling=2, _rotation=4)
+
+
+def _ssim_window(channel, device):
+    """loss_utils.py:26-34 (11x11 Gaussian window, sigma 1.5)"""
+    g = torch.tensor([math.exp(-(x - 5) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+    g = (g / g.sum()).unsqueeze(1)
+    w2 = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0)
+    return w2.expand(channel, 1, 11, 11).contiguous().to(device)
+
+
+def ssim_map(img1, img2, window):
+    """loss_utils.py:36-55"""
+    ch = img1.size(-3)
+    mu1 = F.conv2d(img1, window, padding=5, groups=ch)
+    mu2 = F.conv2d(img2, window, padding=5, groups=ch)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(img1 * img1, window, padding=5, groups=ch) - mu1_sq
+    s2 = F.conv2d(img2 * img2, window, padding=5, groups=ch) - mu2_sq
+    s12 = F.conv2d(img1 * img2, window, padding=5, groups=ch) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    return ((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))
+
+
+def get_loss(weights, pred, gt, window):
+    """loss_utils.py:110-153 with use_sky False"""
+    sky_mask = gt["rgb"].sum(dim=0) == 0.0
+    valid = torch.bitwise_and(~sky_mask, gt["depth"].sum(dim=0) > 0.0)
+    Ll1 = torch.abs((pred["rgb"] - gt["rgb"])[:, valid]).mean()
+    rgb_loss = 0.8 * Ll1 + 0.2 * (1.0 - ssim_map(pred["rgb"], gt["rgb"], window)[:, valid].mean())
+    normal_loss = (1 - (pred["normal"] * pred["surf_normal"]).sum(dim=0)[valid]).mean()
+    alpha_loss = (pred["accum"][:, sky_mask]).mean()
+    weight = 1.0 / gt["depth_cov"]
+    depth_loss = (torch.abs((pred["depth"] - gt["depth"])[:, valid]) * (weight[:, valid])).mean()
+    dist_loss = (pred["dist"][:, valid]).mean()
+    return (weights["rgb_loss"] * rgb_loss + weights["normal_loss"] * normal_loss + weights["alpha_loss"] * alpha_loss +
+            weights["depth_loss"] * depth_loss + weights["dist_loss"] * dist_loss)
+
+
+def depth_propagate_normal(depth, fx, fy, cx, cy):
+    """normal_utils.py:6-21 + tf.py:133-146 (depth -> camera points -> central-difference cross product)"""
+    H, W = depth.shape
+    v, u = torch.meshgrid(torch.arange(H, device=depth.device, dtype=depth.dtype),
+                          torch.arange(W, device=depth.device, dtype=depth.dtype), indexing="ij")
+    pc = torch.stack(((u - cx) / fx * depth, (v - cy) / fy * depth, depth), dim=-1)
+    l2r = pc[1:H - 1, 2:W, :] - pc[1:H - 1, 0:W - 2, :]
+    b2t = pc[0:H - 2, 1:W - 1, :] - pc[2:H, 1:W - 1, :]
+    n = F.normalize(torch.cross(l2r, b2t, dim=-1), p=2, dim=-1)
+    return F.pad(n, pad=(0, 0, 1, 1, 1, 1), mode="constant")
+
+
+class SurfelMapper:
+    """Surfel parameters + optimizer + the per-view training iteration, for a given rasterizer module."""
+
+    def __init__(self, module, scene, device, supervision="rgb+depth", world_size=1, process_group=None):
+        self.mod = module
+        self.device = device
+        self.weights = LOSS_WEIGHTS[supervision]
+        self.W, self.H = scene["W"], scene["H"]
+        self.fx = self.fy = 0.8 * self.W
+        self.cx, self.cy = self.W / 2.0, self.H / 2.0
+        self.world_size = world_size
+        self.pg = process_group
+        self.bg = torch.zeros(3, device=device)
+        self.window = _ssim_window(3, device)
+        self.set_surfels(scene)
+
+    # ---- surfel storage (raw, pre-activation parameters as gaussian_base.py:44-48,55-62) ----
+    def set_surfels(self, scene):
+        dev = self.device
+        P = scene["means3D"].shape[0]
+        raw = dict(_xyz=scene["means3D"], _rgb=scene["colors"],
+                   _opacity=torch.logit(scene["opacities"].clamp(1e-6, 1 - 1e-6)),
+                   _scaling=torch.log(scene["scales"]), _rotation=scene["rotations"])
+        self.P = P
+        for k in GROUPS:
+            setattr(self, k, torch.nn.Parameter(raw[k].to(dev).float().contiguous().requires_grad_(True)))
+        self.optimizer = self.mod.SparseGaussianAdam(
+            [{"params": [getattr(self, k)], "lr": LR[k], "name": k} for k in GROUPS], lr=0.0, eps=1e-15)
+        self._local_scores = torch.zeros(P, 2, device=dev)
+        self._global_scores = torch.zeros(P, 2, device=dev)
+        self._stable_mask = torch.zeros(P, dtype=torch.bool, device=dev)
+        self._globalkf_id = torch.zeros(P, dtype=torch.long, device=dev)
+        self._globalkf_max_scores = torch.zeros(P, device=dev)
+        if self.world_size > 1:
+            # fused gradient buffer: parameter .grad tensors are column blocks of one allocation so that a
+            # single NCCL all-reduce moves gradients, scores and visibility
+            self._fused = torch.zeros(16 * P, device=dev)
+            self._grad_views, off = {}, 0
+            for k in GROUPS:
+                n = GROUP_COLS[k] * P
+                self._grad_views[k] = self._fused[off:off + n].view(P, GROUP_COLS[k])
+                off += n
+            self._score_view = self._fused[off:off + 2 * P].view(P, 2)
+            self._vis_view = self._fused[off + 2 * P:off + 3 * P]
+
+    def params(self):
+        return [getattr(self, k) for k in GROUPS]
+
+    # ---- gaussian_base.py:142-224 ----
+    def render(self, view):
+        """view: dict(viewmatrix, projmatrix, campos on device; tanfovx, tanfovy; w2c [4,4] on device)"""
+        m = self.mod
+        P, H, W = self.P, self.H, self.W
+        screenspace_points = torch.zeros_like(self._xyz, requires_grad=True) + 0
+        try:
+            screenspace_points.retain_grad()
+        except Exception:
+            pass
+        pixel_mask = torch.ones(H * W, dtype=torch.bool, device=self.device)
+        settings = m.GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=view["tanfovx"], tanfovy=view["tanfovy"], bg=self.bg,
+            scale_modifier=1.0, viewmatrix=view["viewmatrix"], projmatrix=view["projmatrix"], sh_degree=0,
+            campos=view["campos"], prefiltered=False, debug=False, pixel_mask=pixel_mask)
+        rasterizer = m.GaussianRasterizer(raster_settings=settings)
+        self._zeros = torch.zeros_like(self._xyz[:, :2]).contiguous().requires_grad_(True)
+        rendered_image, radii, allmap = rasterizer(
+            means3D=self._xyz, means2D=screenspace_points, shs=None, colors_precomp=self._rgb,
+            opacities=torch.sigmoid(self._opacity), scales=torch.exp(self._scaling),
+            rotations=F.normalize(self._rotation), scores=self._zeros, cov3D_precomp=None)
+        w2c = view["w2c"]
+        render_alpha = allmap[1:2]
+        depth = torch.nan_to_num(allmap[0:1] / render_alpha, 0, 0)
+        rets = dict(radii=radii, accum=render_alpha, rgb=rendered_image, depth=depth, dist=allmap[6:7])
+        rets["normal"] = (allmap[2:5].permute(1, 2, 0) @ (w2c[:3, :3])).permute(2, 0, 1)
+        sn = depth_propagate_normal(depth.squeeze(0), self.fx, self.fy, self.cx, self.cy).permute(2, 0, 1)
+        rets["surf_normal"] = (sn.permute(1, 2, 0) @ (w2c[:3, :3])).permute(2, 0, 1)
+        return rets
+
+    # ---- gaussian_base.py:353-404, one iteration ----
+    def train_view(self, view, gt, kf_id=0):
+        """render -> loss -> backward -> score bookkeeping -> weighting_grad -> masked Adam.  Returns the loss
+        tensor (device).  With world_size > 1 every rank calls this with its own view of the window."""
+        dp = self.world_size > 1
+        if dp:
+            self._fused.zero_()
+            for k in GROUPS:
+                getattr(self, k).grad = self._grad_views[k]
+        pred = self.render(view)
+        total_loss = get_loss(self.weights, pred, gt, self.window)
+        total_loss.backward()
+        cur = self._zeros.grad.detach()
+        radii = pred["radii"]
+        if dp:
+            # per-view weighting with this view's scores, applied locally before the reduce (section 8e)
+            self._weighting_grad(cur, torch.clamp(self._global_scores[:, 0] + cur[:, 0], 0, 1e4))
+            self._score_view.copy_(cur)
+            self._vis_view.copy_(radii > 0)
+            torch.distributed.all_reduce(self._fused, group=self.pg)
+            cur = self._score_view
+            self._add_records(cur, kf_id)
+            visible = self._vis_view > 0
+        else:
+            self._add_records(cur, kf_id)
+            self._weighting_grad(cur, self._global_scores[:, 0])
+            visible = radii > 0
+        visible = visible & ~self._stable_mask   # radii[_stable_mask] = 0  (gaussian_base.py:401)
+        self.optimizer.step(visible, self.P)
+        if dp:
+            pass  # grads live in the fused buffer, zeroed at the next call
+        else:
+            self.optimizer.zero_grad()
+        return total_loss.detach()
+
+    def _add_records(self, cur, kf_id):
+        """gaussian_model.py:163-168 and gaussian_base.py:388-392"""
+        self._local_scores[:, 0] += cur[:, 0]
+        self._global_scores[:, 0] += cur[:, 0]
+        large = cur[:, 1] > self._local_scores[:, 1]
+        self._local_scores[:, 1] = torch.where(large, cur[:, 1], self._local_scores[:, 1])
+        self._global_scores = torch.clamp(self._global_scores, 0, 1e4)
+        replace = self._globalkf_max_scores < cur[:, 0]
+        self._globalkf_max_scores = torch.where(replace, cur[:, 0], self._globalkf_max_scores)
+        self._globalkf_id = torch.where(replace, torch.full_like(self._globalkf_id, kf_id), self._globalkf_id)
+
+    def _weighting_grad(self, cur, global_s0):
+        """gaussian_utils.py:56-62; global_s0 already contains this view's score (add_records runs first)"""
+        gw = (cur[:, 0] / (global_s0 + 1e-6 + cur[:, 0])).unsqueeze(1)
+        for k in GROUPS:
+            getattr(self, k).grad.mul_(gw)
+
+
+def view_to_device(view, device, non_blocking=False):
+    """synthetic.View (CPU) -> the dict render() takes; 3 small H2D copies + the w2c pose."""
+    w2c = torch.linalg.inv(view.c2w).float()
+    return dict(viewmatrix=view.viewmatrix.to(device, non_blocking=non_blocking),
+                projmatrix=view.projmatrix.to(device, non_blocking=non_blocking),
+                campos=view.campos.to(device, non_blocking=non_blocking), w2c=w2c.to(device, non_blocking=non_blocking),
+                tanfovx=view.tanfovx, tanfovy=view.tanfovy)

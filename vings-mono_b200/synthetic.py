@@ -160,3 +160,22 @@ def view_inputs(scene, view):
     d.update(viewmatrix=view.viewmatrix, projmatrix=view.projmatrix, campos=view.campos, tanfovx=view.tanfovx,
              tanfovy=view.tanfovy)
     return d
+
+
+def make_gt(scene, view, index):
+    """Ground truth of one window view for the mapping step: box-blurred uniform rgb,
+    the synthetic depth field seen from that pose, unit depth covariance.  The top rows are zeroed so that
+    the loss's sky mask (rgb == 0, loss_utils.py:112) is not empty -- its mean would be NaN otherwise."""
+    cfg = scene["cfg"]
+    W, H = scene["W"], scene["H"]
+    gen = torch.Generator(device="cpu").manual_seed(7000 + 31 * cfg["seed"] + index)
+    rgb = torch.rand(1, 3, H, W, generator=gen)
+    rgb = torch.nn.functional.avg_pool2d(rgb, 5, stride=1, padding=2, count_include_pad=False)[0]
+    sky_rows = max(2, int((0.15 if cfg["outdoor"] else 0.01) * H))
+    rgb[:, :sky_rows, :] = 0.0
+    fx = fy = 0.8 * W
+    v, u = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    dirs = torch.stack([(u.reshape(-1) - W / 2.0) / fx, (v.reshape(-1) - H / 2.0) / fy, torch.ones(H * W)], -1)
+    depth = _depth_field(dirs, cfg["outdoor"], gen).reshape(1, H, W)
+    cov = torch.ones(1, H, W)
+    return dict(rgb=rgb.float().contiguous(), depth=depth.float().contiguous(), depth_cov=cov)
