@@ -69,7 +69,7 @@ size_t sb200_binning_bytes(int64_t R);
 /* per-surfel gradient accumulation scratch for the backward: 80 B * P, zeroed by the library */
 size_t sb200_grad_bytes(int64_t P);
 /* byte offsets of the inspectable arrays inside the workspaces (tests / debugging):
- *   geom:    [0] records float4[5P]  [1] depth f32[P]  [2] tile rect u16x4[P]  [3] tiles_touched u32[P]
+ *   geom:    [0] records float4[8P]  [1] depth f32[P]  [2] tile rect u16x4[P]  [3] tiles_touched u32[P]
  *            [4] point_offsets u32[P] (inclusive)
  *   image:   [0] ranges uint2[tiles] [1] final T,M1,M2 f32[3HW]  [2] n_contrib,median_contrib u32[2HW]
  *   binning: [0] keys A u64[R] (unsorted keys)  [1] keys B u64[R]  [2] values A u32[R]  [3] values B u32[R] */

@@ -151,7 +151,7 @@ def mine_intermediates(mine, inp):
     bo = (ctypes.c_size_t * 4)(); lib.sb200_binning_layout(R, bo)
     g = geom.cpu().numpy(); im = image.cpu().numpy(); b = binning.cpu().numpy()
     fb = lambda buf, off, n, dt: np.frombuffer(buf[off:off + n].tobytes(), dtype=dt)
-    rec = fb(g, go[0], 80 * P, np.float32).reshape(P, 20)
+    rec = fb(g, go[0], 128 * P, np.float32).reshape(P, 32)  # 8 quads, layout in csrc/common.cuh
     N = W * H
     tiles_n = ((W + 15) // 16) * ((H + 15) // 16)
     passes = (32 + _higher_msb(tiles_n) + 7) // 8
@@ -162,8 +162,9 @@ def mine_intermediates(mine, inp):
                 depths=fb(g, go[1], 4 * P, np.float32), rect=fb(g, go[2], 8 * P, np.uint16).reshape(P, 4),
                 tiles_touched=fb(g, go[3], 4 * P, np.uint32), offsets=fb(g, go[4], 4 * P, np.uint32),
                 means2D=np.stack([rec[:, 3], rec[:, 7]], -1),
-                transMat=np.concatenate([rec[:, 0:3], rec[:, 4:7], rec[:, 8:11]], -1),
-                normal_opacity=np.concatenate([rec[:, 12:15], rec[:, 11:12]], -1),
+                transMat=np.concatenate([rec[:, 12:15], rec[:, 16:19], rec[:, 20:23]], -1),
+                normal_opacity=np.concatenate([rec[:, 24:27], rec[:, 15:16]], -1),
+                cull_tau=rec[:, 11], bbox=rec[:, 28:32],
                 keys=keys_sorted, point_list=point_list.cpu().numpy()[:R].view(np.uint32),
                 ranges=fb(im, io[0], 8 * tiles_n, np.uint32).reshape(tiles_n, 2),
                 final_T=fb(im, io[1], 12 * N, np.float32).reshape(3, N),

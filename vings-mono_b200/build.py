@@ -11,11 +11,14 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "build")
-OUT = os.path.join(HERE, "diff_surfel_rasterization", "libsurfel_b200.so")
+# SB200_VARIANT=<name> + SB200_EXTRA_FLAGS="-D..." build a side-by-side debug library (loaded with SB200_LIB)
+VARIANT = os.environ.get("SB200_VARIANT", "")
+OBJ = OBJ + ("_" + VARIANT if VARIANT else "")
+OUT = os.path.join(HERE, "diff_surfel_rasterization", "libsurfel_b200%s.so" % ("_" + VARIANT if VARIANT else ""))
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "radix_sort.cu", "blend_forward.cu", "blend_backward.cu",
            "preprocess_backward.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
-              "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
+              "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + os.environ.get("SB200_EXTRA_FLAGS", "").split()
 
 
 def _stale(target, deps):

@@ -12,12 +12,13 @@
 // a 21-shuffle multi-value butterfly (only when some lane of the warp actually hit the splat), the 8
 // warps' partial sums meet in shared memory, and ONE global atomic per (tile, splat, term) is issued -
 // the same count as the reference's per-bucket-lane atomics, with no 23-register shuffle pipeline.
-#include "common.cuh"
+#include "pair_math.cuh"
 #include <cuda_pipeline.h>
 
 #define BB_THREADS 256
 #define BB_WARPS 8
 #define BB_BATCH 32  // == the reference's bucket size; bucket boundaries are part of the semantics (Q5)
+#define BB_Q 7       // quads 0..6 of the record go to s_q, quad 7 (box) to s_bb
 
 // Multi-value warp reduction: every lane holds v[0..K); afterwards lane L holds in v[0] the warp-wide
 // sum of value slot(L) (or junk if slot(L) < 0).  Each step halves the number of live values.
@@ -67,7 +68,8 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                          const float* __restrict__ out_others, const float* __restrict__ dL_dpixels,
                          const float* __restrict__ dL_dothers, const bool* __restrict__ pixel_mask,
                          float* __restrict__ grad_acc) {
-    __shared__ __align__(16) float4 s_rec[2][BB_BATCH][SB_REC_F4];
+    __shared__ __align__(16) float4 s_q[2][BB_BATCH][BB_Q];
+    __shared__ __align__(16) float4 s_bb[2][BB_BATCH];
     __shared__ uint32_t s_id[2][BB_BATCH];
     __shared__ float s_acc[BB_WARPS][BB_BATCH][SB_GRAD_F];
     __shared__ uint32_t s_wmask[BB_WARPS];
@@ -76,7 +78,16 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t tile = blockIdx.x;
     const uint32_t tx = tile % grid_x, ty = tile / grid_x;
-    const uint32_t px = tx * SB_TILE_X + (tid & 15), py = ty * SB_TILE_Y + (tid >> 4);
+    // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it (as in the forward)
+#ifdef SB_DEBUG_STRIP_MAPPING
+    const uint32_t wx0 = tx * SB_TILE_X, wy0 = ty * SB_TILE_Y + wid * 2;
+    const uint32_t px = wx0 + (lane & 15), py = wy0 + (lane >> 4);
+    const float bx0 = (float)wx0, bx1 = (float)(wx0 + 15), by0 = (float)wy0, by1 = (float)(wy0 + 1);
+#else
+    const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
+    const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
+    const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
+#endif
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
@@ -130,10 +141,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
         const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
         const uint32_t* ids = point_list + range.x + b * BB_BATCH;
         if (tid < cnt * SB_REC_F4) {
-            int sp = tid / SB_REC_F4, q = tid - sp * SB_REC_F4;
+            int sp = tid >> 3, q = tid & 7;
             uint32_t id = __ldg(ids + sp);
             if (q == 0) s_id[b & 1][sp] = id;
-            __pipeline_memcpy_async(&s_rec[b & 1][sp][q], rec + (size_t)id * SB_REC_F4 + q, 16);
+            float4* dst = (q < BB_Q) ? &s_q[b & 1][sp][q] : &s_bb[b & 1][sp];
+            __pipeline_memcpy_async(dst, rec + (size_t)id * SB_REC_F4 + q, 16);
         }
         __pipeline_commit();
     };
@@ -174,59 +186,102 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             ar_reg = reg_f - fin_reg;
             M1b = M1;
             M2b = M2;
-            const float4(*sr)[SB_REC_F4] = s_rec[b & 1];
-            for (int j = 0; j < cnt; j++) {
+            const float4(*sr)[BB_Q] = s_q[b & 1];
+            // warp-level cull: lane tests surfel `lane`'s box against the warp's 8x4 pixel block
+            bool ov = false;
+            if (lane < cnt) {
+                const float4 bb = s_bb[b & 1][lane];
+                ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+            }
+            unsigned vm = __ballot_sync(0xffffffffu, ov);
+#ifdef SB_DEBUG_NO_WARP_CULL
+            vm = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+#endif
+            while (vm) {
+                const int j = __ffs(vm) - 1;
+                vm &= vm - 1;
                 float g[SB_GRAD_F];
 #pragma unroll
                 for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
                 bool hit = false;
-                if ((uint32_t)(b * BB_BATCH + j) < last) {
-                    const float4 q0 = sr[j][0], q1 = sr[j][1], q2 = sr[j][2];
+                // lane-level cull (division free, surfel_math.cuh): outside the alpha >= 1/255 footprint
+                const float4 c0 = sr[j][0], c1 = sr[j][1], c2 = sr[j][2];
+                const float2 d = {c0.w - pixf.x, c1.w - pixf.y};
+                const float r2 = d.x * d.x + d.y * d.y;
+                const float qx = c2.x + c0.x * d.x + c1.x * d.y;
+                const float qy = c2.y + c0.y * d.x + c1.y * d.y;
+                const float qz = c2.z + c0.z * d.x + c1.z * d.y;
+                const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
+#ifdef SB_DEBUG_NO_LANE_CULL
+                const bool culled = false;
+#else
+                const bool culled = E > 0.0f && (r2 + r2) > c2.w;
+#endif
+                if ((uint32_t)(b * BB_BATCH + j) < last && !culled) {
+                    const float4 q0 = sr[j][SB_REC_TU], q1 = sr[j][SB_REC_TV], q2 = sr[j][SB_REC_TW];
                     const float3 Tu = {q0.x, q0.y, q0.z}, Tv = {q1.x, q1.y, q1.z}, Tw = {q2.x, q2.y, q2.z};
-                    const float2 xy = {q0.w, q1.w};
-                    const float opa = q2.w;
-                    float3 k = {pixf.x * Tw.x - Tu.x, pixf.x * Tw.y - Tu.y, pixf.x * Tw.z - Tu.z};
-                    float3 l = {pixf.y * Tw.x - Tv.x, pixf.y * Tw.y - Tv.y, pixf.y * Tw.z - Tv.z};
-                    float3 p = {k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x};
-                    float2 s = {p.x / p.z, p.y / p.z};
-                    float rho3d = (s.x * s.x + s.y * s.y);
-                    float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-                    float rho2d = SB_FILTER_INV_SQUARE * (d.x * d.x + d.y * d.y);
-                    float c_d = (rho3d <= rho2d) ? (s.x * Tw.x + s.y * Tw.y) + Tw.z : Tw.z;
-                    float rho = fminf(rho3d, rho2d);
-                    float power = -0.5f * rho;
+                    const float opa = q0.w;
+                    // pinned geometry (pair_math.cuh): the backward's own rho2d rounding for its gates,
+                    // the forward's for what the forward decided
+                    const SbPair pg = sb_pair(pixf, Tu, Tv, Tw);
+                    const float3 k = pg.k, l = pg.l, p = pg.p;
+                    const float2 s = pg.s;
+                    const float rho3d = pg.rho3d;
+                    const float rho2d = sb_rho2d_backward(d);
+                    const float c_d = sb_pair_depth(pg, rho2d, Tw.z);
+                    const float c_d_fwd = sb_pair_depth(pg, sb_rho2d_forward(d), Tw.z);
+                    const float power = __fmul_rn(fminf(rho3d, rho2d), -0.5f);
+                    float G = 0.f, alpha = 0.f;
+                    bool hit_b = false;  // the reference's backward blends this pair (backward.cu:688-694)
                     if (!(power > 0.0f)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(0.99f, opa * G);
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            hit = true;
-                            const float4 q3 = sr[j][3], q4 = sr[j][4];
-                            const float c[3] = {q3.w, q4.x, q4.y};
-                            const float nrm[3] = {q3.x, q3.y, q3.z};
-                            const float m_d = SB_FAR / (SB_FAR - SB_NEAR) * (1 - SB_NEAR / c_d);
-                            const float dmd_dd = (SB_FAR * SB_NEAR) / ((SB_FAR - SB_NEAR) * c_d * c_d);
-                            // would the forward have skipped this splat?  (forward.cu:408,417)
-                            const bool fwd_skip = (p.z == 0.0f) || (c_d < SB_NEAR);
-                            if (fwd_skip && !div) {
-                                div = true;
-                                Tf = T;
+                        G = expf(power);
+                        alpha = fminf(0.99f, __fmul_rn(G, opa));
+                        hit_b = !(alpha < 1.0f / 255.0f);
+                    }
+                    // did the reference's FORWARD blend it (forward.cu:408-435)?  Same gates plus the
+                    // p.z == 0 / depth < near skips the backward lacks (Q4), with the forward's rho2d rounding.
+                    const float rho2d_f = sb_rho2d_forward(d);
+                    float alpha_f = alpha;
+                    bool contrib_f = hit_b;
+                    if (rho2d_f != rho2d) {  // the two contractions disagree by an ulp: re-evaluate the gate
+                        const float pf = __fmul_rn(fminf(rho3d, rho2d_f), -0.5f);
+                        contrib_f = false;
+                        if (!(pf > 0.0f)) {
+                            alpha_f = fminf(0.99f, __fmul_rn(expf(pf), opa));
+                            contrib_f = !(alpha_f < 1.0f / 255.0f);
+                        }
+                    }
+                    contrib_f = contrib_f && !(p.z == 0.0f) && !(c_d_fwd < SB_NEAR);
+                    if (hit_b || contrib_f) {
+                        const float4 q6 = sr[j][SB_REC_N];
+                        const float c[3] = {q1.w, q2.w, q6.w};
+                        const float nrm[3] = {q6.x, q6.y, q6.z};
+                        // the backward's state leaves the forward's until the next bucket start
+                        if (hit_b != contrib_f && !div) {
+                            div = true;
+                            Tf = T;
 #pragma unroll
-                                for (int i = 0; i < 8; i++) arf[i] = ar[i];
+                            for (int i = 0; i < 8; i++) arf[i] = ar[i];
+                        }
+                        // ---- true forward bookkeeping (moments + distortion prefix) ----
+                        if (contrib_f) {
+                            const float m_f = sb_ndc_depth(c_d_fwd);
+                            const float Tt = div ? Tf : T;
+                            const float wf = alpha_f * Tt;
+                            reg_f += (m_f * m_f * (1 - Tt) + M2 - 2 * m_f * M1) * wf;
+                            M1 += m_f * wf;
+                            M2 += m_f * m_f * wf;
+                            if (div) {
+                                arf[0] += wf * c[0]; arf[1] += wf * c[1]; arf[2] += wf * c[2];
+                                arf[3] += wf * c_d_fwd;  arf[4] += wf;
+                                arf[5] += wf * nrm[0]; arf[6] += wf * nrm[1]; arf[7] += wf * nrm[2];
+                                Tf = Tf * (1 - alpha_f);
                             }
-                            // ---- true forward bookkeeping (moments + distortion prefix) ----
-                            if (!fwd_skip) {
-                                const float Tt = div ? Tf : T;
-                                const float wf = alpha * Tt;
-                                reg_f += (m_d * m_d * (1 - Tt) + M2 - 2 * m_d * M1) * wf;
-                                M1 += m_d * wf;
-                                M2 += m_d * m_d * wf;
-                                if (div) {
-                                    arf[0] += wf * c[0]; arf[1] += wf * c[1]; arf[2] += wf * c[2];
-                                    arf[3] += wf * c_d;  arf[4] += wf;
-                                    arf[5] += wf * nrm[0]; arf[6] += wf * nrm[1]; arf[7] += wf * nrm[2];
-                                    Tf = Tf * (1 - alpha);
-                                }
-                            }
+                        }
+                        if (hit_b) {
+                            hit = true;
+                            const float m_d = sb_ndc_depth(c_d);
+                            const float dmd_dd = (SB_FAR * SB_NEAR) / ((SB_FAR - SB_NEAR) * c_d * c_d);
                             // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
                             const float dchannel_dcolor = alpha * T;
                             const float inv1ma = 1.0f / (1.0f - alpha);

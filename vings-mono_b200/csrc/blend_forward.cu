@@ -1,36 +1,47 @@
 // K3: per-tile front-to-back alpha blending of colour, depth, alpha, normal, median depth, distortion.
 //
 // Replaces renderCUDA (DSR/cuda_rasterizer/forward.cu:254-504).  One CTA per 16x16 tile (the tile
-// size is part of the key contract), one thread per pixel.  Differences from the reference:
-//   * the sorted surfel *records* (80 B, packed once by the preprocess kernel) are gathered with
-//     cp.async 16-B copies into a double-buffered shared-memory ring, so the gather of batch b+1
-//     overlaps the blend of batch b; the reference does 4 scattered array reads + a per-pixel global
-//     colour read per (pixel, surfel);
-//   * no per-32-splat checkpoints are written (the backward re-walks the tile front to back instead),
-//     removing the reference's 13 KiB-per-bucket SampleState traffic entirely;
-//   * termination is tracked per warp (ballot) as well as per CTA.
-// The per-(pixel, surfel) arithmetic keeps the reference's expression order so thresholds
-// (alpha < 1/255, T < 1e-4, T > 0.5, rho3d <= rho2d, depth < near) flip on the same pairs.
-#include "common.cuh"
+// size is part of the key contract); a warp owns an 8x4-pixel block of it, one thread per pixel.
+// The kernel is instruction-issue bound, not HBM bound (profiles/): ~90 % of the (pixel, surfel)
+// pairs a tile list implies contribute nothing, so the design goal is to reject those pairs with as
+// few issued instructions as possible while running the reference's exact arithmetic on the rest:
+//   1. the sorted surfel *records* (128 B = one line, packed once by the preprocess kernel) are
+//      gathered with cp.async 16-B copies into a double-buffered shared-memory ring, so the gather of
+//      batch b+1 overlaps the blend of batch b (the reference does 4 scattered array reads plus a
+//      per-pixel global colour read per pair);
+//   2. warp-level cull: each lane tests ONE surfel's conservative pixel box against the warp's 8x4
+//      block, a ballot compacts the survivors, and only those are visited (1 test per 32 pairs);
+//   3. lane-level cull: a division-free test (6 FFMA for the affine ray-splat cross product + a conic
+//      compare) rejects pixels outside the surfel's alpha >= 1/255 footprint (surfel_math.cuh);
+//   4. pairs that pass run the reference's expression order, so the gates (alpha < 1/255,
+//      T < 1e-4, T > 0.5, rho3d <= rho2d, depth < near) flip on the same pairs;
+//   5. no per-32-splat checkpoints are written (the backward re-walks the tile instead), removing the
+//      reference's 13 KiB-per-bucket SampleState traffic; termination is tracked per warp and per CTA.
+#include "pair_math.cuh"
 #include <cuda_pipeline.h>
 
 #define FB_THREADS 256
 #define FB_BATCH 128
+#define FB_Q 7  // quads 0..6 of the record go to s_q, quad 7 (box) to s_bb
 
 __global__ void __launch_bounds__(FB_THREADS)
 sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                         const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                         float* __restrict__ out_color, float* __restrict__ out_others) {
-    __shared__ __align__(16) float4 s_rec[2][FB_BATCH][SB_REC_F4];
+    __shared__ __align__(16) float4 s_q[2][FB_BATCH][FB_Q];
+    __shared__ __align__(16) float4 s_bb[2][FB_BATCH];
 
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t tile = blockIdx.x;
     const uint32_t tx = tile % grid_x, ty = tile / grid_x;
-    const uint32_t px = tx * SB_TILE_X + (tid & 15), py = ty * SB_TILE_Y + (tid >> 4);
+    // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it
+    const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
+    const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
+    const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
     bool done = !inside;
 
     const uint2 range = ranges[tile];
@@ -41,15 +52,16 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
         const uint32_t* ids = point_list + range.x + b * FB_BATCH;
         for (int e = tid; e < cnt * SB_REC_F4; e += FB_THREADS) {
-            int sp = e / SB_REC_F4, q = e - sp * SB_REC_F4;
+            int sp = e >> 3, q = e & 7;
             uint32_t id = __ldg(ids + sp);
-            __pipeline_memcpy_async(&s_rec[b & 1][sp][q], rec + (size_t)id * SB_REC_F4 + q, 16);
+            float4* dst = (q < FB_Q) ? &s_q[b & 1][sp][q] : &s_bb[b & 1][sp];
+            __pipeline_memcpy_async(dst, rec + (size_t)id * SB_REC_F4 + q, 16);
         }
         __pipeline_commit();
     };
 
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float C[3] = {0.f, 0.f, 0.f};
     float N[3] = {0.f, 0.f, 0.f};
     float D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
@@ -66,59 +78,72 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         // barrier doubles as the CTA-wide termination vote (forward.cu:348-350)
         if (__syncthreads_count(done) == FB_THREADS) break;
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
-        if (!__all_sync(0xffffffffu, done)) {
-            const float4(*sr)[SB_REC_F4] = s_rec[b & 1];
-            for (int j = 0; j < cnt && !done; j++) {
-                contributor++;
-                const float4 q0 = sr[j][0], q1 = sr[j][1], q2 = sr[j][2];
-                const float3 Tu = {q0.x, q0.y, q0.z}, Tv = {q1.x, q1.y, q1.z}, Tw = {q2.x, q2.y, q2.z};
-                const float2 xy = {q0.w, q1.w};
-                // two homogeneous planes through the pixel, intersected with the splat (forward.cu:405-412)
-                float3 k = {pixf.x * Tw.x - Tu.x, pixf.x * Tw.y - Tu.y, pixf.x * Tw.z - Tu.z};
-                float3 l = {pixf.y * Tw.x - Tv.x, pixf.y * Tw.y - Tv.y, pixf.y * Tw.z - Tv.z};
-                float3 p = {k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x};
-                if (p.z == 0.0f) continue;
-                float2 s = {p.x / p.z, p.y / p.z};
-                float rho3d = (s.x * s.x + s.y * s.y);
-                float2 d = {xy.x - pixf.x, xy.y - pixf.y};
-                float rho2d = SB_FILTER_INV_SQUARE * (d.x * d.x + d.y * d.y);
-                float rho = fminf(rho3d, rho2d);
-                float depth = (rho3d <= rho2d) ? (s.x * Tw.x + s.y * Tw.y) + Tw.z : Tw.z;
+        const float4(*sq)[FB_Q] = s_q[b & 1];
+        const float4* sbb = s_bb[b & 1];
+        for (int c = 0; c < cnt; c += 32) {
+            if (__all_sync(0xffffffffu, done)) break;
+            // ---- warp-level cull: lane tests surfel c+lane's box against the warp's pixel block ----
+            bool ov = false;
+            if (c + lane < cnt) {
+                const float4 bb = sbb[c + lane];
+                ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+            }
+            unsigned m = __ballot_sync(0xffffffffu, ov);
+            while (m) {
+                const int j = c + __ffs(m) - 1;
+                m &= m - 1;
+                // ---- lane-level cull (division free) ----
+                const float4 c0 = sq[j][0], c1 = sq[j][1], c2 = sq[j][2];
+                const float2 d = {c0.w - pixf.x, c1.w - pixf.y};  // == the reference's d (forward.cu:413)
+                const float r2 = d.x * d.x + d.y * d.y;
+                const float qx = c2.x + c0.x * d.x + c1.x * d.y;
+                const float qy = c2.y + c0.y * d.x + c1.y * d.y;
+                const float qz = c2.z + c0.z * d.x + c1.z * d.y;
+                const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
+                if (done || (E > 0.0f && (r2 + r2) > c2.w)) continue;
+                // ---- the reference's arithmetic (forward.cu:401-468) ----
+                const float4 q3 = sq[j][SB_REC_TU], q4 = sq[j][SB_REC_TV], q5 = sq[j][SB_REC_TW];
+                const float3 Tu = {q3.x, q3.y, q3.z}, Tv = {q4.x, q4.y, q4.z}, Tw = {q5.x, q5.y, q5.z};
+                const SbPair g = sb_pair(pixf, Tu, Tv, Tw);
+                if (g.p.z == 0.0f) continue;
+                const float rho2d = sb_rho2d_forward(d);
+                const float rho = fminf(g.rho3d, rho2d);
+                const float depth = sb_pair_depth(g, rho2d, Tw.z);
                 if (depth < SB_NEAR) continue;
-                float opa = q2.w;
-                float power = -0.5f * rho;
+                const float power = __fmul_rn(rho, -0.5f);
                 if (power > 0.0f) continue;
-                float alpha = fminf(0.99f, opa * expf(power));
+                const float alpha = fminf(0.99f, __fmul_rn(q3.w, expf(power)));
                 if (alpha < 1.0f / 255.0f) continue;
-                float test_T = T * (1 - alpha);
+                const float test_T = __fmul_rn(T, __fadd_rn(-alpha, 1.0f));
                 if (test_T < 0.0001f) {
                     done = true;
                     continue;
                 }
-                float w = alpha * T;
-                const float4 q3 = sr[j][3], q4 = sr[j][4];
-                // distortion, depth, moments (forward.cu:444-449)
-                float A = 1 - T;
-                float m = SB_FAR / (SB_FAR - SB_NEAR) * (1 - SB_NEAR / depth);
-                distortion += (m * m * A + M2 - 2 * m * M1) * w;
-                D += depth * w;
-                M1 += m * w;
-                M2 += m * m * w;
-                if (T > 0.5) {
+                const float w = __fmul_rn(T, alpha);
+                const float4 q6 = sq[j][SB_REC_N];
+                const uint32_t contributor = (uint32_t)(b * FB_BATCH + j + 1);
+                // distortion, depth, moments (forward.cu:444-449), in the oracle build's operation order
+                const float A = __fadd_rn(-T, 1.0f);
+                const float mm = sb_ndc_depth(depth);
+                const float m2 = __fmul_rn(mm, mm);
+                const float e = __fmaf_rn(-M1, __fadd_rn(mm, mm), __fmaf_rn(A, m2, M2));
+                distortion = __fmaf_rn(w, e, distortion);
+                D = __fmaf_rn(depth, w, D);
+                M1 = __fmaf_rn(w, mm, M1);
+                M2 = __fmaf_rn(w, m2, M2);
+                if (T > 0.5f) {
                     median_depth = depth;
                     median_contributor = contributor;
                 }
-                N[0] += q3.x * w;
-                N[1] += q3.y * w;
-                N[2] += q3.z * w;
-                C[0] += q3.w * w;
-                C[1] += q4.x * w;
-                C[2] += q4.y * w;
+                N[0] = __fmaf_rn(q6.x, w, N[0]);
+                N[1] = __fmaf_rn(q6.y, w, N[1]);
+                N[2] = __fmaf_rn(q6.z, w, N[2]);
+                C[0] = __fmaf_rn(q4.w, w, C[0]);
+                C[1] = __fmaf_rn(q5.w, w, C[1]);
+                C[2] = __fmaf_rn(q6.w, w, C[2]);
                 T = test_T;
                 last_contributor = contributor;
             }
-            // a pixel that left the loop early still has to count the rest of the batch
-            // (contributor is only used while !done, so no fix-up is needed)
         }
         __syncthreads();  // everyone finished reading buffer b&1 before batch b+2 lands in it
     }

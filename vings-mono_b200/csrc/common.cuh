@@ -17,13 +17,24 @@
 #define SB_FAR 100.0f   // DSR/cuda_rasterizer/auxiliary.h:38
 #define SB_FILTER_INV_SQUARE 2.0f  // auxiliary.h:39
 
-// Per-surfel render record: 5 x float4 = 80 B, 16-B aligned, fetched as one unit by the blend kernels.
-//   q0 = (Tu.x, Tu.y, Tu.z, xy.x)
-//   q1 = (Tv.x, Tv.y, Tv.z, xy.y)
-//   q2 = (Tw.x, Tw.y, Tw.z, opacity)
-//   q3 = (n.x,  n.y,  n.z,  r)
-//   q4 = (g,    b,    depth, 0)
-#define SB_REC_F4 5
+// Per-surfel render record: 8 x float4 = 128 B = one cache line, fetched as one unit by the blend
+// kernels.  Quads 0-2 feed the division-free cull test, 3-6 the exact reference arithmetic, 7 the
+// warp-level bounding-box test.
+//   q0 = (A.x,  A.y,  A.z,  xy.x)      p(pixel) = C + A*dx + B*dy with (dx,dy) = xy - pixel, where
+//   q1 = (B.x,  B.y,  B.z,  xy.y)      p = (px*Tw - Tu) x (py*Tw - Tv) is affine in the pixel
+//   q2 = (C.x,  C.y,  C.z,  tau)       tau = padded cutoff: alpha >= 1/255 needs min(rho3d,rho2d) <= tau
+//   q3 = (Tu.x, Tu.y, Tu.z, opacity)
+//   q4 = (Tv.x, Tv.y, Tv.z, r)
+//   q5 = (Tw.x, Tw.y, Tw.z, g)
+//   q6 = (n.x,  n.y,  n.z,  b)
+//   q7 = (xmin, xmax, ymin, ymax)      pixel-space box outside of which the surfel cannot reach alpha >= 1/255
+#define SB_REC_F4 8
+#define SB_REC_CULL 0
+#define SB_REC_TU 3
+#define SB_REC_TV 4
+#define SB_REC_TW 5
+#define SB_REC_N 6
+#define SB_REC_BBOX 7
 
 // Per-surfel gradient accumulation record (floats), filled by the backward blend kernel with
 // atomics and consumed by the backward preprocess kernel.

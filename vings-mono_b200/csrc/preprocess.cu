@@ -6,6 +6,7 @@
 // loads; rotations are natural float4s.  Each CTA publishes its tile-count aggregate and resolves
 // its exclusive prefix by decoupled look-back, so offsets are written by the same kernel.
 #include "surfel_math.cuh"
+#include "surfel_math_pinned.cuh"
 
 #define PRE_THREADS 256
 
@@ -60,17 +61,22 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
         int radius_i = 0;
         float3 p_orig = {s_mean[3 * threadIdx.x], s_mean[3 * threadIdx.x + 1], s_mean[3 * threadIdx.x + 2]};
         // near cull only (auxiliary.h:197-222); p_hom/p_proj of the reference are dead code
-        float pz = s_vm[2] * p_orig.x + s_vm[6] * p_orig.y + s_vm[10] * p_orig.z + s_vm[14];
+        // operation order of the oracle build (FMUL on the m6*y term, auxiliary.h:91-99 as nvcc contracts it)
+        float pz = __fadd_rn(__fmaf_rn(p_orig.z, s_vm[10], __fmaf_rn(p_orig.x, s_vm[2], __fmul_rn(p_orig.y, s_vm[6]))),
+                             s_vm[14]);
         if (!(pz <= 0.2f)) {
-            SbMat3 T;
+            float Tm[9];
             float3 normal;
-            sb_compute_transmat(p_orig, __ldg(scales + idx), __ldg(rotations + idx), s_pm, s_vm, W, H, T, normal);
-            float2 point_image, extent;
-            if (sb_compute_aabb(T, point_image, extent)) {
-                float radius = 3.0f * ceilf(fmaxf(extent.x, extent.y));
+            const float4 rot = __ldg(rotations + idx);
+            const float2 scl = __ldg(scales + idx);
+            sb_transmat_pinned(rot.x, rot.y, rot.z, rot.w, scl.x, scl.y, p_orig.x, p_orig.y, p_orig.z, s_pm, s_vm, W, H,
+                               Tm, normal);
+            float2 point_image;
+            float radius;
+            if (sb_aabb_pinned(Tm, point_image, radius)) {
                 uint2 rmin, rmax;
                 uint2 grid = {(unsigned)((W + SB_TILE_X - 1) / SB_TILE_X), (unsigned)((H + SB_TILE_Y - 1) / SB_TILE_Y)};
-                sb_get_rect(point_image, radius, rmin, rmax, grid);
+                sb_rect_pinned(point_image, (int)radius, grid, rmin, rmax);
                 uint32_t area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
                 if (area != 0) {
                     touched = area;
@@ -78,12 +84,20 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
                     depths[idx] = pz;
                     rects[idx] = make_ushort4((unsigned short)rmin.x, (unsigned short)rmin.y,
                                               (unsigned short)rmax.x, (unsigned short)rmax.y);
+                    const float opa = __ldg(opacities + idx);
+                    const float3 Tu = {Tm[0], Tm[1], Tm[2]};
+                    const float3 Tv = {Tm[3], Tm[4], Tm[5]};
+                    const float3 Tw = {Tm[6], Tm[7], Tm[8]};
+                    SbCull cull = sb_cull_data(Tu, Tv, Tw, point_image, opa);
                     float4* r = rec + (size_t)idx * SB_REC_F4;
-                    r[0] = make_float4(T.c[0][0], T.c[0][1], T.c[0][2], point_image.x);
-                    r[1] = make_float4(T.c[1][0], T.c[1][1], T.c[1][2], point_image.y);
-                    r[2] = make_float4(T.c[2][0], T.c[2][1], T.c[2][2], __ldg(opacities + idx));
-                    r[3] = make_float4(normal.x, normal.y, normal.z, s_col[3 * threadIdx.x]);
-                    r[4] = make_float4(s_col[3 * threadIdx.x + 1], s_col[3 * threadIdx.x + 2], pz, 0.f);
+                    r[0] = make_float4(cull.A.x, cull.A.y, cull.A.z, point_image.x);
+                    r[1] = make_float4(cull.B.x, cull.B.y, cull.B.z, point_image.y);
+                    r[2] = make_float4(cull.C.x, cull.C.y, cull.C.z, cull.tau);
+                    r[3] = make_float4(Tu.x, Tu.y, Tu.z, opa);
+                    r[4] = make_float4(Tv.x, Tv.y, Tv.z, s_col[3 * threadIdx.x]);
+                    r[5] = make_float4(Tw.x, Tw.y, Tw.z, s_col[3 * threadIdx.x + 1]);
+                    r[6] = make_float4(normal.x, normal.y, normal.z, s_col[3 * threadIdx.x + 2]);
+                    r[7] = cull.bbox;
                 }
             }
         }

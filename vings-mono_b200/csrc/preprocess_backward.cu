@@ -130,7 +130,7 @@ sb_preprocess_backward_kernel(int P, int Wq, int Hq, const float* __restrict__ m
         o_mean3D = make_float3(dL_dM[2][0], dL_dM[2][1], dL_dM[2][2]);
         // densification heuristic replaces the screen-space gradient (Q9, :1041-1044); uses the raw
         // accumulated dL/dTu.z, dL/dTv.z and the *forward* Tw.z
-        const float depth = rec[(size_t)idx * SB_REC_F4 + 2].z;
+        const float depth = rec[(size_t)idx * SB_REC_F4 + SB_REC_TW].z;
         o_mean2D.x = a[2] * depth * 0.5 * float(Wq);
         o_mean2D.y = a[5] * depth * 0.5 * float(Hq);
         o_color = make_float3(a[15], a[16], a[17]);

@@ -189,3 +189,61 @@ __device__ __forceinline__ void sb_get_rect(float2 p, int max_radius, uint2& rec
     rect_max.x = min(grid.x, max((int)0, (int)((p.x + max_radius + SB_TILE_X - 1) / SB_TILE_X)));
     rect_max.y = min(grid.y, max((int)0, (int)((p.y + max_radius + SB_TILE_Y - 1) / SB_TILE_Y)));
 }
+
+// ---- conservative culling data (new; no counterpart in the reference) -----------------------------
+// A (pixel, surfel) pair can only contribute if alpha = min(0.99, opa*exp(-rho/2)) >= 1/255 with
+// rho = min(rho3d, rho2d) (forward.cu:412-435), i.e. rho <= 2 ln(255 opa).  The blend kernels skip a
+// pair without running the reference arithmetic when BOTH rho3d and rho2d are provably above a padded
+// cutoff tau; pairs that pass are evaluated with the reference's exact expression order, so skipping
+// never changes a result.
+//  * rho3d > tau  <=>  p.x^2 + p.y^2 > tau p.z^2 where p = (px Tw - Tu) x (py Tw - Tv) is AFFINE in the
+//    pixel:  p = Tu x Tv + px (Tv x Tw) + py (Tw x Tu).  Re-centred on the surfel's screen centre xy and
+//    with (dx,dy) = xy - pixel:  p = C + A dx + B dy.  Scaled by 1/|C.z| (the test is homogeneous).
+//  * the screen-space box of {rho3d <= tau} follows compute_aabb (forward.cu:130-157) with the cutoff
+//    weights (tau, tau, -1); it is united with the low-pass disk {rho2d <= tau} and padded by a pixel.
+struct SbCull {
+    float3 A, B, C;
+    float tau;
+    float4 bbox;  // xmin, xmax, ymin, ymax in pixel coordinates (pixel centres are integers)
+};
+
+__device__ __forceinline__ float3 sb_cross(float3 a, float3 b) {
+    return make_float3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+
+__device__ __forceinline__ SbCull sb_cull_data(float3 Tu, float3 Tv, float3 Tw, float2 xy, float opa) {
+    SbCull c;
+    const float BIG = 1e30f;
+    // padded cutoff: 1% + 0.01 covers the rounding of the affine form against the reference's k x l
+    float t = 255.0f * opa;
+    float tau = t > 1.0f ? 2.0f * logf(t) : 0.0f;
+    tau = 1.01f * tau + 0.01f;
+    c.tau = tau;
+    float3 a = sb_cross(Tv, Tw), b = sb_cross(Tw, Tu), c0 = sb_cross(Tu, Tv);
+    // p at the pixel (xy - d) = c0 + (xy.x - dx) a + (xy.y - dy) b
+    float3 C = make_float3(c0.x + xy.x * a.x + xy.y * b.x, c0.y + xy.x * a.y + xy.y * b.y, c0.z + xy.x * a.z + xy.y * b.z);
+    float n = 1.0f / fmaxf(fabsf(C.z), 1e-30f);
+    c.A = make_float3(-a.x * n, -a.y * n, -a.z * n);
+    c.B = make_float3(-b.x * n, -b.y * n, -b.z * n);
+    c.C = make_float3(C.x * n, C.y * n, C.z * n);
+    // box of the tau-level ellipse
+    float xmin = -BIG, xmax = BIG, ymin = -BIG, ymax = BIG;
+    float dist = tau * (Tw.x * Tw.x + Tw.y * Tw.y) - Tw.z * Tw.z;
+    if (dist < 0.0f) {
+        float inv = 1.0f / dist;
+        float fx = tau * inv, fz = -inv;
+        float cx = fx * (Tu.x * Tw.x + Tu.y * Tw.y) + fz * Tu.z * Tw.z;
+        float cy = fx * (Tv.x * Tw.x + Tv.y * Tw.y) + fz * Tv.z * Tw.z;
+        float hx = cx * cx - (fx * (Tu.x * Tu.x + Tu.y * Tu.y) + fz * Tu.z * Tu.z);
+        float hy = cy * cy - (fx * (Tv.x * Tv.x + Tv.y * Tv.y) + fz * Tv.z * Tv.z);
+        if (hx >= 0.0f && hy >= 0.0f) {  // false for NaN
+            // pad: one pixel + a relative term for the cancellation in cx*cx - (...)
+            float ex = sqrtf(hx) + 1.0f + 1e-3f * fabsf(cx), ey = sqrtf(hy) + 1.0f + 1e-3f * fabsf(cy);
+            xmin = cx - ex; xmax = cx + ex; ymin = cy - ey; ymax = cy + ey;
+        }
+    }
+    float rd = sqrtf(0.5f * tau) + 0.5f;  // low-pass disk rho2d = 2 |xy - pixel|^2 <= tau
+    c.bbox = make_float4(fminf(xmin, xy.x - rd), fmaxf(xmax, xy.x + rd), fminf(ymin, xy.y - rd), fmaxf(ymax, xy.y + rd));
+    if (!(c.bbox.x <= c.bbox.y) || !(c.bbox.z <= c.bbox.w)) c.bbox = make_float4(-BIG, BIG, -BIG, BIG);
+    return c;
+}

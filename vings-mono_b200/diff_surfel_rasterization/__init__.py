@@ -22,7 +22,7 @@ import torch
 import torch.nn as nn
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libsurfel_b200.so")
+_LIB_PATH = os.environ.get("SB200_LIB") or os.path.join(_HERE, "libsurfel_b200.so")  # SB200_LIB: debug variants
 _lib = None
 
 _vp = ctypes.c_void_p
