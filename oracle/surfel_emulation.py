@@ -119,10 +119,17 @@ def _get_rect(xy, radius_i, grid_x, grid_y):
     return lo(xy[:, 0], grid_x), lo(xy[:, 1], grid_y), hi(xy[:, 0], grid_x), hi(xy[:, 1], grid_y)
 
 
+def _fma32(a, b, c):
+    """fp32 fused multiply-add: the product is exact in float64, one rounding to float32 at the end."""
+    return (a.double() * b.double() + c.double()).float()
+
+
 def preprocess(means3D, scales, rotations, opacities, view, proj, W, H):
     P = means3D.shape[0]
     vm = view.reshape(16)
-    pz = vm[2] * means3D[:, 0] + vm[6] * means3D[:, 1] + vm[10] * means3D[:, 2] + vm[14]
+    # View depth with the FMA contraction of the CUDA build (FMUL on m6*y, then two FFMAs, then FADD): its bits
+    # are the low word of the sort key, so ties between equal-depth surfels must break as on the GPU.
+    pz = _fma32(means3D[:, 2], vm[10], _fma32(means3D[:, 0], vm[2], means3D[:, 1] * vm[6])) + vm[14]
     T, L, R, _ = _transmat(means3D, scales, rotations, proj, W, H)
     normal, _ = _view_normal(L, view)
     Tu, Tv, Tw = T[:, 0, :], T[:, 1, :], T[:, 2, :]

@@ -113,7 +113,20 @@ def ref_intermediates(ref, inp):
     n_contrib, off = take(im, off, 8 * N, np.uint32)
     ranges, off = take(im, off, 8 * N, np.uint32)
     tiles_n = ((W + 15) // 16) * ((H + 15) // 16)
-    return dict(R=R, B=B, color=color.cpu(), allmap=others.cpu(), radii=radii.cpu().numpy(), depths=depths,
+    # max_contrib sits one (128-B aligned) N-word array before pixel_colors, which is a copy of out_color
+    # (rasterizer_impl.cu:258-259,474); the cub scan scratch in between has an unknown size, so search for it
+    max_contrib = None
+    want = color.cpu().numpy().tobytes()
+    o = _a128(off)
+    for _ in range(1 << 16):
+        if o + len(want) > len(im):
+            break
+        if im[o:o + len(want)].tobytes() == want:
+            o_mc = o - _a128(4 * N)
+            max_contrib = np.frombuffer(im[o_mc:o_mc + 4 * tiles_n].tobytes(), dtype=np.uint32)
+            break
+        o += 128
+    return dict(R=R, B=B, max_contrib=max_contrib, color=color.cpu(), allmap=others.cpu(), radii=radii.cpu().numpy(), depths=depths,
                 means2D=means2D.reshape(P, 2), transMat=transMat.reshape(P, 9), normal_opacity=nrm_opa.reshape(P, 4),
                 tiles_touched=tiles, point_list=point_list, vals_unsorted=vals_unsorted, keys=keys,
                 keys_unsorted=keys_unsorted, final_T=accum.reshape(3, N), n_contrib=n_contrib.reshape(2, N),
@@ -184,3 +197,28 @@ def _higher_msb(n):
 def rel_err(a, b):
     a, b = a.double(), b.double()
     return float((a - b).abs().sum() / b.abs().sum().clamp(min=1e-30))
+
+
+def tainted_surfels(ri, W, H):
+    """Surfels whose reference gradient is garbage-dependent (reference quirk Q17): the
+    reference's forward reduces `max_contrib` with cub::BlockReduce<uint32_t, 256> on a 16x16 block
+    (forward.cu:496-502), which mis-indexes the warp aggregates, so the stored value is max(rows 0-1 of the
+    tile, stale shared memory) rather than the tile maximum; its backward then drops every 32-surfel bucket
+    starting at or beyond that value (backward.cu:503).  Returns (ids of the surfels sitting in dropped
+    buckets that some pixel still needs, number of affected tiles)."""
+    mc = ri["max_contrib"]
+    if mc is None:
+        raise RuntimeError("max_contrib not located in the reference image buffer")
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    last = np.zeros((gy * 16, gx * 16), np.int64)
+    last[:H, :W] = ri["n_contrib"][0].reshape(H, W)
+    true_max = last.reshape(gy, 16, gx, 16).max(axis=(1, 3)).reshape(-1)
+    need = (true_max + 31) // 32           # buckets some pixel needs
+    done = (mc.astype(np.int64) + 31) // 32  # buckets the reference processes
+    ids = []
+    bad = np.nonzero(done < need)[0]
+    for t in bad:
+        r0, r1 = ri["ranges"][t]
+        ids.append(ri["point_list"][int(r0) + 32 * int(done[t]):int(r1)])
+    ids = np.unique(np.concatenate(ids)) if ids else np.zeros(0, np.int64)
+    return ids.astype(np.int64), len(bad)

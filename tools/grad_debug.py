@@ -32,3 +32,11 @@ if "--emu" in sys.argv:
     for i in worst.tolist():
         print(i, "emu score", grads["scores"][i].tolist())
     print("emu vs ref rel", util.rel_err(grads["scores"], orf["d_scores"]), "emu vs mine", util.rel_err(grads["scores"], om["d_scores"]))
+ri = util.ref_intermediates(ref, inp)
+ids, nbad = util.tainted_surfels(ri, inp["W"], inp["H"])
+print("reference max_contrib bug: affected tiles", nbad, "tainted surfels", len(ids))
+keep = torch.ones(om["d_scores"].shape[0], dtype=torch.bool)
+keep[torch.from_numpy(ids)] = False
+for k in ("d_means3D", "d_means2D", "d_colors", "d_opacities", "d_scales", "d_rotations", "d_scores"):
+    print("  untainted %-12s rel %.3e  maxabs %.3e" % (k, util.rel_err(om[k][keep], orf[k][keep]),
+                                                  float((om[k][keep] - orf[k][keep]).abs().max())))

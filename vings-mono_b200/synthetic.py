@@ -81,7 +81,7 @@ def _depth_field(dirs, outdoor, gen):
     return (z * (1.0 + noise)).clamp(zmin, zmax)
 
 
-def make_scene(name, P=None, K=None):
+def make_scene(name, P=None, K=None, W=None, H=None):
     """Returns dict(means3D, scales, rotations, opacities, colors) as CPU fp32 tensors (already the
     *activated* values the mapper hands to the rasterizer) and the list of window views."""
     cfg = dict(CONFIGS[name])
@@ -89,6 +89,10 @@ def make_scene(name, P=None, K=None):
         cfg["P"] = P
     if K is not None:
         cfg["K"] = K
+    if W is not None:
+        cfg["W"] = W
+    if H is not None:
+        cfg["H"] = H
     P, W, H = cfg["P"], cfg["W"], cfg["H"]
     gen = torch.Generator(device="cpu").manual_seed(cfg["seed"])
     fx = fy = 0.8 * W
