@@ -107,7 +107,7 @@ class SurfelMapper:
                    _scaling=torch.log(scene["scales"]), _rotation=scene["rotations"])
         self.P = P
         for k in GROUPS:
-            setattr(self, k, torch.nn.Parameter(raw[k].to(dev).float().contiguous().requires_grad_(True)))
+            setattr(self, k, torch.nn.Parameter(raw[k].to(dev).float().contiguous().clone().requires_grad_(True)))
         self.optimizer = self.mod.SparseGaussianAdam(
             [{"params": [getattr(self, k)], "lr": LR[k], "name": k} for k in GROUPS], lr=0.0, eps=1e-15)
         self._local_scores = torch.zeros(P, 2, device=dev)
