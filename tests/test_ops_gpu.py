@@ -75,11 +75,13 @@ def test_adam_matches_reference_kernel(mine):
                                vp(vis.data_ptr()), 1e-3, 0.9, 0.999, 1e-15, N, M, vp(torch.cuda.current_stream().cuda_stream))
     assert rc == 0
     # adam.cu:26-37 restated
-    m2 = torch.where(vis[:, None], 0.9 * m0 + (1 - 0.9) * g, m0)
-    v2 = torch.where(vis[:, None], 0.999 * v0 + (1 - 0.999) * g * g, v0)
+    b1, b2 = torch.tensor(0.9, device="cuda"), torch.tensor(0.999, device="cuda")   # fp32 constants: 1 - 0.999f != 0.001
+    m2 = torch.where(vis[:, None], b1 * m0 + (1.0 - b1) * g, m0)
+    v2 = torch.where(vis[:, None], b2 * v0 + (1.0 - b2) * g * g, v0)
     p2 = torch.where(vis[:, None], p0 - 1e-3 * m2 / (v2.sqrt() + 1e-15), p0)
-    assert torch.allclose(m1, m2, rtol=1e-6, atol=1e-8) and torch.allclose(v1, v2, rtol=1e-6, atol=1e-10)
-    assert torch.allclose(p1, p2, rtol=1e-6, atol=1e-7)
+    # torch evaluates the same formulas with different FMA contraction -> a few ulp
+    assert torch.allclose(m1, m2, rtol=1e-5, atol=1e-7) and torch.allclose(v1, v2, rtol=1e-5, atol=1e-9)
+    assert torch.allclose(p1, p2, rtol=1e-5, atol=1e-6)
     assert torch.equal(p1[~vis], p0[~vis]) and torch.equal(m1[~vis], m0[~vis])   # invisible rows untouched
     if ref is not None:
         p3, m3, v3 = p0.clone(), m0.clone(), v0.clone()
@@ -105,6 +107,7 @@ def test_mark_visible(mine):
     ref = util.load_ref()
     scene, views = synthetic.make_scene("C3", P=50_000)
     inp = util.cuda_inputs(synthetic.view_inputs(scene, views[0]))
+    inp["means3D"][::3, 2] *= -1.0     # a third of the cloud behind the camera
     rast = mine.GaussianRasterizer(util.make_settings(mine, inp))
     got = rast.markVisible(inp["means3D"])
     vm = inp["viewmatrix"].reshape(16)
