@@ -47,6 +47,9 @@ def parse():
     ap.add_argument("--config", default="C2")
     ap.add_argument("--surfels", type=int, default=0, help="override P (debug only; makes the line invalid)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--unfused", action="store_true",
+                    help="b200 arm: torch autograd + torch loss around the drop-in rasterizer instead of the fused "
+                         "mapping blocks (debug / ablation)")
     return ap.parse_args()
 
 
@@ -126,6 +129,11 @@ def stage_bytes(stage, c):
         "blend_bwd": 4 * R + 76 * V + 101 * HW + 80 * V,
         "preprocess_bwd": 156 * V + 72 * P,
         "adam": 28 * 13 * V + P,
+        # fused mapping blocks: loss = rendered maps 40 + ground truth 20 in, gradients 40 out;
+        # activate = 28 in + 28 out; update = bookkeeping 49/surfel + (13 grads + 39 param/moment rw) per visible
+        "map_loss": 100 * HW,
+        "activate": 56 * P,
+        "update": 49 * P + 364 * V,
     }[stage]
 
 
@@ -192,7 +200,8 @@ def main():
     scene, views = synthetic.make_scene(args.config, P=args.surfels or None)
     K = len(views)
     W, H, P = scene["W"], scene["H"], scene["means3D"].shape[0]
-    mapper = mapper_step.SurfelMapper(mod, scene, dev, supervision=cfg["sup"], world_size=world, process_group=pg)
+    mapper = mapper_step.SurfelMapper(mod, scene, dev, supervision=cfg["sup"], world_size=world, process_group=pg,
+                                      fused=False if (args.unfused or args.impl == "reference") else None)
 
     # window ground truth: pinned host copies (e2e leg) and device copies (value leg)
     gt_host = [{k: v.pin_memory() for k, v in synthetic.make_gt(scene, views[i], i).items()} for i in range(K)]
@@ -280,6 +289,8 @@ def main():
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": "%s: KITTI-shaped mapping step, %d surfels, %d-keyframe window at %dx%d, %s loss; "
                                "one step = %d views per rank" % (args.config, P, K, W, H, cfg["sup"], VIEWS_PER_STEP),
+                   "mapping_step": "fused (activate, rasterizer, map_loss, surfel_update kernels)" if mapper.fused
+                                   else "torch autograd + torch loss around the rasterizer module",
                    "surfels": P, "window": K, "width": W, "height": H, "views_per_step_per_rank": VIEWS_PER_STEP,
                    "parallelism": "window views partitioned over %d rank(s), surfels replicated, fused [P,16] "
                                   "gradient all-reduce (NCCL)" % world if world > 1 else "single GPU",

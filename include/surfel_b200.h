@@ -53,7 +53,10 @@ enum {
     SB200_STAGE_BLEND_BWD = 5,      /* per-tile backward blend (+ zeroing of its accumulation record) */
     SB200_STAGE_PREPROCESS_BWD = 6, /* per-surfel backward preprocess */
     SB200_STAGE_ADAM = 7,           /* masked Adam update */
-    SB200_NUM_STAGES = 8
+    SB200_STAGE_MAP_LOSS = 8,       /* fused mapping loss (5 kernels) */
+    SB200_STAGE_ACTIVATE = 9,       /* raw parameters -> rasterizer inputs */
+    SB200_STAGE_UPDATE = 10,        /* fused per-surfel update (activation backward, records, weighting, Adam) */
+    SB200_NUM_STAGES = 11
 };
 int sb200_profile_enable(int on);
 int sb200_profile_read(double ms[SB200_NUM_STAGES], long long count[SB200_NUM_STAGES]);
@@ -117,6 +120,54 @@ int sb200_mark_visible(int P, const float* means3D, const float* viewmatrix, con
 int sb200_adam_update(float* param, const float* param_grad, float* exp_avg, float* exp_avg_sq,
                       const uint8_t* visible /* bool [N] */, float lr, float b1, float b2, float eps,
                       uint32_t N, uint32_t M, void* stream);
+
+/* ---- the mapping step either side of the rasterizer -----------
+ * These replace torch code of the CALLER (scripts/gaussian/), not entry points of the reference extension;
+ * the reference-side binding is the Python in vings-mono_b200/diff_surfel_rasterization/mapping.py.
+ *
+ * sb200_map_loss: get_loss (scripts/gaussian/loss_utils.py:110-153, use_sky False) on the rasterizer's raw
+ * outputs, including render_raw's post-processing (scripts/gaussian/gaussian_base.py:205-221: depth =
+ * nan_to_num(allmap0/allmap1), normals rotated by w2c[:3,:3], depth_propagate_normal of
+ * scripts/gaussian/normal_utils.py:6-21) and the backward of all of it.
+ *   color [3,H,W], allmap [7,H,W]: sb200_forward_finish outputs; gt_rgb [3,H,W], gt_depth [H,W], gt_depth_cov [H,W];
+ *   w2c: 16 floats, row-major 4x4 world->camera pose (device);
+ *   (cx, cy, fx, fy): camera point of pixel (col, row) at depth d is ((col-cx)/fx*d, (row-cy)/fy*d, d).  In the
+ *   reference's naming u is the ROW: cx = intrinsic cv, fx = fv, cy = cu, fy = fu (scripts/gaussian/tf.py:139-143,
+ *   configs/rtg/hotel.yaml:31-34);
+ *   ws: sb200_map_loss_bytes(W, H) bytes of scratch;
+ *   loss [7] (device): total, then the six means (L1, SSIM, normal, alpha, depth, dist; normal is 0 when
+ *   w_normal == 0).  Means over an empty pixel set are NaN, like torch's;
+ *   dL_dcolor [3,H,W], dL_dallmap [7,H,W]: fully written.  Where allmap1 == 0 torch's autograd yields NaN for
+ *   dL_dallmap[0:2] (0/0); no surfel is blended there, and 0 is written instead. */
+size_t sb200_map_loss_bytes(int W, int H);
+int sb200_map_loss(int W, int H, const float* color, const float* allmap, const float* gt_rgb, const float* gt_depth,
+                   const float* gt_depth_cov, const float* w2c, float cx, float cy, float fx, float fy,
+                   float w_rgb, float w_normal, float w_alpha, float w_depth, float w_dist,
+                   void* ws, float* loss, float* dL_dcolor, float* dL_dallmap, void* stream);
+
+/* sb200_activate: opacities = sigmoid(opacity_raw) [P], scales = exp(scaling_raw) [P,2], rotations =
+ * normalize(rotation_raw) [P,4] (scripts/gaussian/gaussian_base.py:160-166 via the model's activations). */
+int sb200_activate(int P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                   float* opacities, float* scales, float* rotations, void* stream);
+
+/* sb200_surfel_update: one pass over the surfels after sb200_backward: backward of the three activations,
+ * add_records (scripts/gaussian/gaussian_model.py:163-168, gaussian_base.py:388-392), weighting_grad
+ * (scripts/gaussian/gaussian_utils.py:56-62), radii[_stable_mask] = 0 and SparseGaussianAdam.step(radii > 0)
+ * (gaussian_base.py:400-403) for the five groups, in the order xyz[3], rgb[3], opacity[1], scaling[2], rotation[4].
+ *   params / exp_avg / exp_avg_sq: HOST arrays of 5 device pointers; lr: HOST array of 5 floats;
+ *   d_*: sb200_backward outputs (gradients w.r.t. the activated inputs); cur_scores [P,2] its scores output;
+ *   local_scores, global_scores [P,2], kf_max_scores [P], kf_id int64 [P]: the mapper's score bookkeeping; kf =
+ *   id of the current keyframe.
+ * mode SB200_UPDATE_LOCAL does all of it.  For views sharded over ranks, SB200_UPDATE_DP_PRE writes the weighted
+ * raw-parameter gradients, the scores and the visibility into fused [16,P] (column blocks 3,3,1,2,4 | 2 | 1) for
+ * ONE all-reduce(sum), and SB200_UPDATE_DP_POST does the bookkeeping and Adam from the reduced buffer. */
+enum { SB200_UPDATE_LOCAL = 0, SB200_UPDATE_DP_PRE = 1, SB200_UPDATE_DP_POST = 2 };
+int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+                        const float* d_means3D, const float* d_colors, const float* d_opacity, const float* d_scales,
+                        const float* d_rotations, const float* cur_scores, const int* radii,
+                        const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
+                        int64_t* kf_id, int64_t kf, float* fused, const float* lr, float b1, float b2, float eps,
+                        void* stream);
 
 /* ---- building blocks exposed for parity tests ----------------------------------------------- */
 /* Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0,end_bit).  keys_in/vals_in are

@@ -1,0 +1,201 @@
+"""Rows N1/N2 of SURVEY.md section 8f: the fused mapping loss and the fused per-surfel update.
+
+Oracles:
+* tests/golden/loss_*.npz -- produced by the reference's own Python (scripts/gaussian/loss_utils.get_loss,
+  normal_utils.depth_propagate_normal, tf.TFer) by tests/golden/make_loss_golden.py;
+* mapper_step.SurfelMapper(fused=False) -- the torch restatement of the caller (itself checked against the
+  golden vectors here, on CPU) driving the same rasterizer.
+Tolerances are fp32 rounding: the fused kernels sum in a different association (separable filter, block
+reductions) than torch's conv2d / masked means.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import mapper_step
+import synthetic
+import util
+
+GOLDEN_LOSS = ("loss_rgb_depth", "loss_normal_dist")
+WKEYS = ("rgb_loss", "normal_loss", "alpha_loss", "depth_loss", "dist_loss")
+
+
+def load_loss_case(name):
+    z = np.load(os.path.join(util.GOLDEN, name + ".npz"))
+    c = {k: torch.from_numpy(z[k]) for k in ("color", "allmap", "gt_rgb", "gt_depth", "gt_cov", "w2c", "g_color",
+                                              "g_allmap")}
+    c["loss"] = float(z["loss"])
+    fu, fv, cu, cv = [float(x) for x in z["intr"]]
+    c.update(fx=fv, fy=fu, cx=cv, cy=cu)  # the reference's u is the row (configs/rtg/hotel.yaml:31-34)
+    c["weights"] = {k: float(w) for k, w in zip(WKEYS, z["weights"])}
+    return c
+
+
+def torch_loss(c, dev="cpu"):
+    """mapper_step's restatement of render_raw post-processing + get_loss, with autograd."""
+    color = c["color"].to(dev).clone().requires_grad_(True)
+    allmap = c["allmap"].to(dev).clone().requires_grad_(True)
+    w2c = c["w2c"].to(dev)
+    alpha = allmap[1:2]
+    depth = torch.nan_to_num(allmap[0:1] / alpha, 0, 0)
+    pred = dict(accum=alpha, rgb=color, depth=depth, dist=allmap[6:7])
+    pred["normal"] = (allmap[2:5].permute(1, 2, 0) @ w2c[:3, :3]).permute(2, 0, 1)
+    sn = mapper_step.depth_propagate_normal(depth.squeeze(0), c["fx"], c["fy"], c["cx"], c["cy"]).permute(2, 0, 1)
+    pred["surf_normal"] = (sn.permute(1, 2, 0) @ w2c[:3, :3]).permute(2, 0, 1)
+    gt = dict(rgb=c["gt_rgb"].to(dev), depth=c["gt_depth"].to(dev), depth_cov=c["gt_cov"].to(dev))
+    loss = mapper_step.get_loss(c["weights"], pred, gt, mapper_step._ssim_window(3, dev))
+    loss.backward()
+    return float(loss.detach()), color.grad, allmap.grad
+
+
+@pytest.mark.parametrize("name", GOLDEN_LOSS)
+def test_torch_restatement_matches_reference_loss(name):
+    """The caller-side torch code of mapper_step (used by the reference arm of bench.py and by fused=False)
+    reproduces the reference's get_loss and its gradients."""
+    c = load_loss_case(name)
+    loss, g_color, g_allmap = torch_loss(c)
+    assert abs(loss - c["loss"]) <= 1e-6 * max(1.0, abs(c["loss"]))
+    assert torch.equal(torch.isnan(g_allmap), torch.isnan(c["g_allmap"]))
+    assert util.rel_err(g_color, c["g_color"]) < 1e-6
+    assert util.rel_err(torch.nan_to_num(g_allmap), torch.nan_to_num(c["g_allmap"])) < 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", GOLDEN_LOSS)
+def test_map_loss_matches_reference_golden(name):
+    mine = util.load_mine()
+    c = load_loss_case(name)
+    cu = lambda k: c[k].cuda()
+    loss, g_color, g_allmap = mine.mapping.map_loss(cu("color"), cu("allmap"), cu("gt_rgb"), cu("gt_depth"),
+                                                    cu("gt_cov"), cu("w2c"), c["cx"], c["cy"], c["fx"], c["fy"],
+                                                    c["weights"])
+    assert abs(float(loss[0]) - c["loss"]) <= 2e-6 * max(1.0, abs(c["loss"]))
+    assert torch.isfinite(g_color).all() and torch.isfinite(g_allmap).all()
+    assert util.rel_err(g_color.cpu(), c["g_color"]) < 2e-5
+    ref = c["g_allmap"]
+    nan = torch.isnan(ref)
+    # torch yields NaN (0/0) where no surfel covers the pixel; the kernel writes 0 there (surfel_b200.h)
+    # (channel 0 gets 0; channel 1 keeps its finite alpha-loss term)
+    assert not nan[2:].any() and torch.equal(nan[0], nan[1])
+    assert float(g_allmap[0].cpu()[nan[0]].abs().max()) == 0.0
+    sky = c["gt_rgb"].sum(0) == 0
+    expect = torch.where(sky, torch.full_like(ref[1], c["weights"]["alpha_loss"] / float(sky.sum())), torch.zeros_like(ref[1]))
+    assert torch.allclose(g_allmap[1].cpu()[nan[1]], expect[nan[1]], rtol=1e-6, atol=0)
+    for ch in range(7):
+        r, m = ref[ch][~nan[ch]], g_allmap[ch].cpu()[~nan[ch]]
+        assert util.rel_err(m, r) < 2e-5, (ch, util.rel_err(m, r))
+        assert float((m - r).abs().max()) <= 1e-5 * max(float(r.abs().max()), 1e-12) + 1e-9, ch
+
+
+@pytest.mark.gpu
+def test_map_loss_edge_cases():
+    """No valid pixel / no sky pixel: means over empty sets are NaN like torch's, gradients stay finite zeros."""
+    mine = util.load_mine()
+    c = load_loss_case("loss_rgb_depth")
+    gt_rgb = c["gt_rgb"].clone()
+    gt_rgb[:, :4, :] = 0.5  # no sky
+    out = mine.mapping.map_loss(c["color"].cuda(), c["allmap"].cuda(), gt_rgb.cuda(), c["gt_depth"].cuda(),
+                                c["gt_cov"].cuda(), c["w2c"].cuda(), c["cx"], c["cy"], c["fx"], c["fy"], c["weights"])
+    assert torch.isnan(out[0][0]) and torch.isnan(out[0][4]) and torch.isfinite(out[0][1])
+    assert torch.isfinite(out[1]).all() and torch.isfinite(out[2]).all()
+    out = mine.mapping.map_loss(c["color"].cuda(), c["allmap"].cuda(), torch.zeros_like(c["gt_rgb"]).cuda(),
+                                c["gt_depth"].cuda(), c["gt_cov"].cuda(), c["w2c"].cuda(), c["cx"], c["cy"], c["fx"],
+                                c["fy"], c["weights"])
+    assert torch.isnan(out[0][0])
+    assert float(out[1].abs().max()) == 0.0  # no valid pixel: no colour gradient
+    assert torch.isfinite(out[2]).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", GOLDEN_LOSS)
+def test_map_loss_full_size_matches_torch(name):
+    """At C2's image size against the torch restatement on the GPU (random maps)."""
+    mine = util.load_mine()
+    c = load_loss_case(name)
+    W, H = 1241, 376
+    g = torch.Generator(device="cpu").manual_seed(5)
+    alpha = torch.rand(H, W, generator=g).clamp(0.05, 0.999)
+    alpha[torch.rand(H, W, generator=g) < 0.02] = 0.0
+    yy, xx = torch.meshgrid(torch.arange(H, dtype=torch.float32), torch.arange(W, dtype=torch.float32), indexing="ij")
+    depth = 3.0 + 0.01 * xx + 0.02 * yy + torch.sin(xx / 30.0) + 0.02 * torch.rand(H, W, generator=g)
+    allmap = torch.zeros(7, H, W)
+    allmap[0], allmap[1] = depth * alpha, alpha
+    allmap[2:5] = torch.nn.functional.normalize(torch.randn(3, H, W, generator=g), dim=0) * alpha
+    allmap[6] = 0.01 * torch.rand(H, W, generator=g)
+    color = torch.rand(3, H, W, generator=g)
+    gt_rgb = (0.5 * color + 0.5 * torch.rand(3, H, W, generator=g))
+    gt_rgb[:, :50] = 0.0
+    gt_depth = (depth + 0.1 * torch.randn(H, W, generator=g)).unsqueeze(0)
+    gt_depth[0][torch.rand(H, W, generator=g) < 0.1] = 0.0
+    big = dict(c, color=color, allmap=allmap, gt_rgb=gt_rgb, gt_depth=gt_depth, gt_cov=0.5 + torch.rand(1, H, W, generator=g),
+               fx=0.8 * W, fy=0.8 * W, cx=W / 2.0, cy=H / 2.0)
+    loss_t, gc_t, ga_t = torch_loss(big, dev="cuda")
+    loss, g_color, g_allmap = mine.mapping.map_loss(color.cuda(), allmap.cuda(), gt_rgb.cuda(), gt_depth.cuda(),
+                                                    big["gt_cov"].cuda(), c["w2c"].cuda(), big["cx"], big["cy"],
+                                                    big["fx"], big["fy"], c["weights"])
+    assert abs(float(loss[0]) - loss_t) <= 1e-5 * max(1.0, abs(loss_t))
+    assert util.rel_err(g_color, gc_t) < 1e-4
+    nan = torch.isnan(ga_t)
+    assert util.rel_err(torch.where(nan, torch.zeros_like(ga_t), g_allmap), torch.nan_to_num(ga_t)) < 1e-4
+
+
+@pytest.mark.gpu
+def test_activate_matches_torch():
+    mine = util.load_mine()
+    g = torch.Generator(device="cpu").manual_seed(3)
+    o = (3 * torch.randn(5000, 1, generator=g)).cuda()
+    s = (torch.randn(5000, 2, generator=g) - 3).cuda()
+    r = torch.randn(5000, 4, generator=g).cuda()
+    r[7] = 0.0
+    ao, as_, ar = mine.mapping.activate(o, s, r)
+    assert torch.allclose(ao, torch.sigmoid(o), rtol=2e-7, atol=1e-9)
+    assert torch.allclose(as_, torch.exp(s), rtol=2e-7, atol=0)
+    assert torch.allclose(ar, torch.nn.functional.normalize(r), rtol=1e-6, atol=1e-7)
+
+
+def _mapper_pair(mine, sup, P=20000, n_views=3, stable_frac=0.1):
+    scene, views = synthetic.make_scene("C3", P=P, W=160, H=96)
+    dev = torch.device("cuda")
+    a = mapper_step.SurfelMapper(mine, scene, dev, supervision=sup, fused=False)
+    b = mapper_step.SurfelMapper(mine, scene, dev, supervision=sup, fused=True)
+    g = torch.Generator(device="cpu").manual_seed(1)
+    stable = (torch.rand(P, generator=g) < stable_frac).cuda()
+    a._stable_mask, b._stable_mask = stable.clone(), stable.clone()
+    init = {k: getattr(a, k).data.clone() for k in mapper_step.GROUPS}
+    losses = []
+    for i in range(n_views):
+        v = views[-1 - (i % len(views))]
+        gt = {k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()}
+        vd = mapper_step.view_to_device(v, dev)
+        losses.append((float(a.train_view(vd, gt, kf_id=i + 1)), float(b.train_view(vd, gt, kf_id=i + 1))))
+    return a, b, losses, init
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sup", ["rgb+depth", "rgb+depth+normal+dist"])
+def test_fused_view_matches_torch_view(sup):
+    """Three training views from the same start: torch autograd + torch loss + 5 Adam launches vs the fused
+    path.  Parameters move by lr-sized steps whose direction is sign-like (Adam), so moments and scores are the
+    sensitive quantities."""
+    mine = util.load_mine()
+    a, b, losses, init = _mapper_pair(mine, sup)
+    for la, lb in losses:
+        assert abs(la - lb) <= 2e-5 * max(1.0, abs(la)), losses
+    for k in mapper_step.GROUPS:
+        pa, pb = getattr(a, k).data, getattr(b, k).data
+        sa, sb = a.optimizer.state[getattr(a, k)], b.optimizer.state[getattr(b, k)]
+        assert util.rel_err(sb["exp_avg"], sa["exp_avg"]) < 2e-3, (k, util.rel_err(sb["exp_avg"], sa["exp_avg"]))
+        assert util.rel_err(sb["exp_avg_sq"], sa["exp_avg_sq"]) < 2e-3, k
+        assert float((pa - init[k]).abs().sum()) > 0, k
+        assert float((pa - pb).abs().max()) <= 2.5 * mapper_step.LR[k] * 3, (k, float((pa - pb).abs().max()))
+        assert util.rel_err(pb, pa) < 1e-5, k
+    assert util.rel_err(b._local_scores, a._local_scores) < 1e-4
+    assert util.rel_err(b._global_scores, a._global_scores) < 1e-4
+    assert util.rel_err(b._globalkf_max_scores, a._globalkf_max_scores) < 1e-4
+    assert float((a._globalkf_id != b._globalkf_id).float().mean()) < 1e-3
+    # surfels frozen by _stable_mask did not move
+    st = a._stable_mask
+    assert torch.equal(b._xyz.data[st], init["_xyz"][st])
+    assert not torch.equal(b._xyz.data[~st], init["_xyz"][~st])

@@ -30,23 +30,21 @@ static cudaEvent_t prof_event() {
     return e;
 }
 
-struct StageScope {
-    bool on; int stage; cudaStream_t s; cudaEvent_t e0;
-    StageScope(int stage_, cudaStream_t s_) : on(false), stage(stage_), s(s_), e0(nullptr) {
-        std::lock_guard<std::mutex> g(g_prof_mu);
-        if (!g_prof_on) return;
-        on = true;
-        e0 = prof_event();
-        cudaEventRecord(e0, s);
-    }
-    ~StageScope() {
-        if (!on) return;
-        std::lock_guard<std::mutex> g(g_prof_mu);
-        cudaEvent_t e1 = prof_event();
-        cudaEventRecord(e1, s);
-        g_prof_recs.push_back({stage, e0, e1});
-    }
-};
+SbStageScope::SbStageScope(int stage_, cudaStream_t s_) : on(false), stage(stage_), s(s_), e0(nullptr) {
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    if (!g_prof_on) return;
+    on = true;
+    e0 = prof_event();
+    cudaEventRecord(e0, s);
+}
+SbStageScope::~SbStageScope() {
+    if (!on) return;
+    std::lock_guard<std::mutex> g(g_prof_mu);
+    cudaEvent_t e1 = prof_event();
+    cudaEventRecord(e1, s);
+    g_prof_recs.push_back({stage, e0, e1});
+}
+typedef SbStageScope StageScope;
 
 void sb_set_error(const char* fmt, ...) {
     va_list ap;
@@ -57,7 +55,7 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 2; }
+int sb200_abi_version(void) { return 3; }
 
 long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -228,6 +226,37 @@ int sb200_adam_update(float* param, const float* param_grad, float* exp_avg, flo
     StageScope sc(SB200_STAGE_ADAM, (cudaStream_t)stream);
     return sb_launch_adam(param, param_grad, exp_avg, exp_avg_sq, (const bool*)visible, lr, b1, b2, eps, N, M,
                           (cudaStream_t)stream);
+}
+
+size_t sb200_map_loss_bytes(int W, int H) { return sb_map_loss_bytes(W, H); }
+
+int sb200_map_loss(int W, int H, const float* color, const float* allmap, const float* gt_rgb, const float* gt_depth,
+                   const float* gt_depth_cov, const float* w2c, float cx, float cy, float fx, float fy, float w_rgb,
+                   float w_normal, float w_alpha, float w_depth, float w_dist, void* ws, float* loss,
+                   float* dL_dcolor, float* dL_dallmap, void* stream) {
+    g_err[0] = 0;
+    if (W <= 0 || H <= 0) { sb_set_error("map_loss: bad dimensions %dx%d", W, H); return 1; }
+    if (!color || !allmap || !gt_rgb || !gt_depth || !gt_depth_cov || !w2c || !ws || !loss || !dL_dcolor || !dL_dallmap) {
+        sb_set_error("map_loss: NULL input");
+        return 1;
+    }
+    StageScope sc(SB200_STAGE_MAP_LOSS, (cudaStream_t)stream);
+    return sb_launch_map_loss(W, H, color, allmap, gt_rgb, gt_depth, gt_depth_cov, w2c, cx, cy, fx, fy, w_rgb,
+                              w_normal, w_alpha, w_depth, w_dist, (char*)ws, loss, dL_dcolor, dL_dallmap,
+                              (cudaStream_t)stream);
+}
+
+int sb200_activate(int P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                   float* opacities, float* scales, float* rotations, void* stream) {
+    g_err[0] = 0;
+    if (P < 0) { sb_set_error("activate: bad P"); return 1; }
+    if (P > 0 && (!opacity_raw || !scaling_raw || !rotation_raw || !opacities || !scales || !rotations)) {
+        sb_set_error("activate: NULL input");
+        return 1;
+    }
+    StageScope sc(SB200_STAGE_ACTIVATE, (cudaStream_t)stream);
+    return sb_launch_activate(P, opacity_raw, scaling_raw, rotation_raw, opacities, scales, rotations,
+                              (cudaStream_t)stream);
 }
 
 int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, uint64_t* keys_out, uint32_t* vals_out, void* stream) {

@@ -142,6 +142,12 @@ static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
 
 void sb_set_error(const char* fmt, ...);
 void sb_count_launch(int n);  // kernels launched (reported as gpu_launches by bench.py)
+// Optional per-stage device timing (api.cu): brackets a stage with CUDA events on its launching stream.
+struct SbStageScope {
+    bool on; int stage; cudaStream_t s; cudaEvent_t e0;
+    SbStageScope(int stage, cudaStream_t s);
+    ~SbStageScope();
+};
 #define SB_CUDA_CHECK(expr)                                                              \
     do {                                                                                 \
         cudaError_t _e = (expr);                                                         \
@@ -173,5 +179,12 @@ int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanf
                                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
                                   float* dL_dscales, float* dL_drotations, float* dL_dtransMat, float* scores,
                                   cudaStream_t s);
+size_t sb_map_loss_bytes(int W, int H);
+int sb_launch_map_loss(int W, int H, const float* color, const float* allmap, const float* gt_rgb,
+                       const float* gt_depth, const float* gt_cov, const float* w2c, float cx, float cy, float fx,
+                       float fy, float w_rgb, float w_norm, float w_alpha, float w_depth, float w_dist, char* ws,
+                       float* loss, float* dL_dcolor, float* dL_dallmap, cudaStream_t s);
+int sb_launch_activate(int P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                       float* opacities, float* scales, float* rotations, cudaStream_t s);
 int sb_launch_adam(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, const bool* visible,
                    float lr, float b1, float b2, float eps, uint32_t N, uint32_t M, cudaStream_t s);

@@ -1,0 +1,211 @@
+// N1: everything the mapping step does per surfel around the rasterizer, fused.
+//
+//   sb_activate_kernel        raw parameters -> rasterizer inputs: sigmoid(opacity), exp(scaling),
+//                             normalize(rotation)                       (scripts/gaussian/gaussian_base.py:160-166)
+//   sb_surfel_update_kernel   one pass over the surfels after the rasterizer's backward:
+//       backward of those three activations (what autograd does for the reference),
+//       add_records score bookkeeping              (scripts/gaussian/gaussian_model.py:163-168, gaussian_base.py:388-392)
+//       weighting_grad                             (scripts/gaussian/gaussian_utils.py:56-62)
+//       radii[_stable_mask] = 0; SparseGaussianAdam.step(radii > 0) for the five parameter groups
+//                                                  (gaussian_base.py:400-403, DSR/cuda_rasterizer/adam.cu:9-38)
+// The reference runs ~45 P-sized torch kernels plus five Adam launches for this; here every array is read
+// and written once (13 parameters + 26 moments + 13 gradients + bookkeeping ~ 230 B per visible surfel).
+//
+// Multi-GPU (views sharded over ranks) splits the pass around the all-reduce:
+//   SB_UPD_DP_PRE   activation backward + per-view weighting, written with scores and visibility into the
+//                   fused [16,P] buffer that NCCL reduces;
+//   SB_UPD_DP_POST  bookkeeping + Adam from the reduced buffer.
+#include "common.cuh"
+#include "../../include/surfel_b200.h"
+
+__global__ void sb_activate_kernel(int P, const float* __restrict__ opacity_raw, const float2* __restrict__ scaling_raw,
+                                   const float4* __restrict__ rotation_raw, float* __restrict__ opacities,
+                                   float2* __restrict__ scales, float4* __restrict__ rotations) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    opacities[i] = 1.0f / (1.0f + expf(-opacity_raw[i]));
+    const float2 s = scaling_raw[i];
+    scales[i] = make_float2(expf(s.x), expf(s.y));
+    const float4 q = rotation_raw[i];
+    const float den = fmaxf(sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w), 1e-12f);  // F.normalize eps
+    rotations[i] = make_float4(q.x / den, q.y / den, q.z / den, q.w / den);
+}
+
+int sb_launch_activate(int P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                       float* opacities, float* scales, float* rotations, cudaStream_t s) {
+    if (P == 0) return 0;
+    sb_activate_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, opacity_raw, (const float2*)scaling_raw,
+                                                       (const float4*)rotation_raw, opacities, (float2*)scales,
+                                                       (float4*)rotations);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+struct SbUpdateArgs {
+    // raw parameters and Adam moments, group order: xyz[3] rgb[3] opacity[1] scaling[2] rotation[4]
+    float* param[5];
+    float* m[5];
+    float* v[5];
+    // gradients w.r.t. the rasterizer inputs (activated), as sb200_backward writes them
+    const float* d_means3D; const float* d_colors; const float* d_opacity; const float* d_scales; const float* d_rot;
+    const float* cur_scores;   // [P,2] this view's scores
+    const int* radii;          // [P]
+    const uint8_t* stable;     // [P] bool
+    float* local_scores;       // [P,2]
+    float* global_scores;      // [P,2]
+    float* kf_max;             // [P]
+    long long* kf_id;          // [P]
+    float* fused;              // [16,P] column blocks (DP modes) or NULL
+    float lr[5];
+    float b1, b2, eps;
+    long long kf;
+    int P, mode;
+};
+
+__device__ __forceinline__ void sb_adam1(float* p, float* m, float* v, size_t i, float g, float lr, float b1, float b2,
+                                         float eps) {
+    float mm = m[i], vv = v[i];
+    mm = b1 * mm + (1.0f - b1) * g;
+    vv = b2 * vv + (1.0f - b2) * g * g;
+    p[i] += -lr * mm / (sqrtf(vv) + eps);
+    m[i] = mm;
+    v[i] = vv;
+}
+
+static const int GRP_COLS[5] = {3, 3, 1, 2, 4};
+__constant__ int c_grp_off[5] = {0, 3, 6, 7, 9};  // column offsets of the groups inside the fused buffer
+
+__global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int P = a.P;
+    if (i >= P) return;
+    const size_t Pz = (size_t)P;
+    float g[13];
+    float cur0, cur1;
+    bool visible;
+    if (a.mode == SB200_UPDATE_DP_POST) {
+        // reduced gradients, score sums and visibility counts come back in the fused buffer
+#pragma unroll
+        for (int grp = 0, c = 0; grp < 5; grp++) {
+            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
+            const float* blk = a.fused + (size_t)c_grp_off[grp] * Pz;
+            for (int k = 0; k < nc; k++, c++) g[c] = blk[(size_t)i * nc + k];
+        }
+        cur0 = a.fused[13 * Pz + 2 * (size_t)i];
+        cur1 = a.fused[13 * Pz + 2 * (size_t)i + 1];
+        visible = a.fused[15 * Pz + i] > 0.0f;
+    } else {
+        cur0 = a.cur_scores[2 * (size_t)i];
+        cur1 = a.cur_scores[2 * (size_t)i + 1];
+        visible = a.radii[i] > 0;
+        // ---- backward of the activations ----
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            g[k] = a.d_means3D[3 * (size_t)i + k];
+            g[3 + k] = a.d_colors[3 * (size_t)i + k];
+        }
+        const float y = 1.0f / (1.0f + expf(-a.param[2][i]));
+        g[6] = a.d_opacity[i] * (1.0f - y) * y;
+        g[7] = a.d_scales[2 * (size_t)i] * expf(a.param[3][2 * (size_t)i]);
+        g[8] = a.d_scales[2 * (size_t)i + 1] * expf(a.param[3][2 * (size_t)i + 1]);
+        const float4 q = ((const float4*)a.param[4])[i];
+        const float4 dq = ((const float4*)a.d_rot)[i];
+        const float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        if (len > 1e-12f) {
+            const float4 r = make_float4(q.x / len, q.y / len, q.z / len, q.w / len);
+            const float rd = r.x * dq.x + r.y * dq.y + r.z * dq.z + r.w * dq.w;
+            g[9] = (dq.x - r.x * rd) / len; g[10] = (dq.y - r.y * rd) / len;
+            g[11] = (dq.z - r.z * rd) / len; g[12] = (dq.w - r.w * rd) / len;
+        } else {
+            g[9] = dq.x / 1e-12f; g[10] = dq.y / 1e-12f; g[11] = dq.z / 1e-12f; g[12] = dq.w / 1e-12f;
+        }
+    }
+
+    // ---- add_records ----
+    float glob0 = a.global_scores[2 * (size_t)i];
+    if (a.mode != SB200_UPDATE_DP_PRE) {
+        a.local_scores[2 * (size_t)i] += cur0;
+        const float l1 = a.local_scores[2 * (size_t)i + 1];
+        if (cur1 > l1) a.local_scores[2 * (size_t)i + 1] = cur1;
+        glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);
+        a.global_scores[2 * (size_t)i] = glob0;
+        a.global_scores[2 * (size_t)i + 1] = fminf(fmaxf(a.global_scores[2 * (size_t)i + 1], 0.0f), 1e4f);
+        if (a.kf_max[i] < cur0) {
+            a.kf_max[i] = cur0;
+            a.kf_id[i] = a.kf;
+        }
+    } else {
+        glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);  // this view's score counted, nothing stored yet
+    }
+
+    // ---- weighting_grad ----
+    if (a.mode != SB200_UPDATE_DP_POST) {
+        const float gw = cur0 / (glob0 + 1e-6f + cur0);
+#pragma unroll
+        for (int c = 0; c < 13; c++) g[c] *= gw;
+    }
+
+    if (a.mode == SB200_UPDATE_DP_PRE) {
+#pragma unroll
+        for (int grp = 0, c = 0; grp < 5; grp++) {
+            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
+            float* blk = a.fused + (size_t)c_grp_off[grp] * Pz;
+            for (int k = 0; k < nc; k++, c++) blk[(size_t)i * nc + k] = g[c];
+        }
+        a.fused[13 * Pz + 2 * (size_t)i] = cur0;
+        a.fused[13 * Pz + 2 * (size_t)i + 1] = cur1;
+        a.fused[15 * Pz + i] = visible ? 1.0f : 0.0f;
+        return;
+    }
+
+    // ---- masked Adam ----
+    if (visible && !a.stable[i]) {
+#pragma unroll
+        for (int grp = 0, c = 0; grp < 5; grp++) {
+            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
+            for (int k = 0; k < nc; k++, c++)
+                sb_adam1(a.param[grp], a.m[grp], a.v[grp], (size_t)i * nc + k, g[c], a.lr[grp], a.b1, a.b2, a.eps);
+        }
+    }
+}
+
+int sb_launch_surfel_update(const SbUpdateArgs& a, cudaStream_t s) {
+    if (a.P == 0) return 0;
+    (void)GRP_COLS;
+    sb_surfel_update_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(a);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp_avg,
+                                   float* const* exp_avg_sq, const float* d_means3D, const float* d_colors,
+                                   const float* d_opacity, const float* d_scales, const float* d_rotations,
+                                   const float* cur_scores, const int* radii, const uint8_t* stable_mask,
+                                   float* local_scores, float* global_scores, float* kf_max_scores, int64_t* kf_id,
+                                   int64_t kf, float* fused, const float* lr, float b1, float b2, float eps,
+                                   void* stream) {
+    if (P < 0 || mode < 0 || mode > 2) { sb_set_error("surfel_update: bad P/mode"); return 1; }
+    if (!params || !exp_avg || !exp_avg_sq || !lr || !global_scores) { sb_set_error("surfel_update: NULL input"); return 1; }
+    if (mode != SB200_UPDATE_LOCAL && !fused) { sb_set_error("surfel_update: DP modes need the fused buffer"); return 1; }
+    if (mode != SB200_UPDATE_DP_POST &&
+        (!d_means3D || !d_colors || !d_opacity || !d_scales || !d_rotations || !cur_scores || !radii)) {
+        sb_set_error("surfel_update: NULL gradient input");
+        return 1;
+    }
+    if (mode != SB200_UPDATE_DP_PRE && (!stable_mask || !local_scores || !kf_max_scores || !kf_id)) {
+        sb_set_error("surfel_update: NULL bookkeeping input");
+        return 1;
+    }
+    SbUpdateArgs a;
+    for (int g = 0; g < 5; g++) {
+        a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g];
+    }
+    a.d_means3D = d_means3D; a.d_colors = d_colors; a.d_opacity = d_opacity; a.d_scales = d_scales; a.d_rot = d_rotations;
+    a.cur_scores = cur_scores; a.radii = radii; a.stable = stable_mask;
+    a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores; a.kf_id = (long long*)kf_id;
+    a.fused = fused; a.b1 = b1; a.b2 = b2; a.eps = eps; a.kf = kf; a.P = P; a.mode = mode;
+    SbStageScope sc(SB200_STAGE_UPDATE, (cudaStream_t)stream);
+    return sb_launch_surfel_update(a, (cudaStream_t)stream);
+}

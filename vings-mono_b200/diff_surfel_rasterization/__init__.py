@@ -73,7 +73,16 @@ def _load():
     lib.sb200_profile_enable.argtypes = [_i32]
     lib.sb200_profile_read.restype = _i32
     lib.sb200_profile_read.argtypes = [ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong)]
-    if lib.sb200_abi_version() != 2:
+    lib.sb200_map_loss_bytes.restype = _sz
+    lib.sb200_map_loss_bytes.argtypes = [_i32, _i32]
+    lib.sb200_map_loss.restype = _i32
+    lib.sb200_map_loss.argtypes = [_i32, _i32] + [_vp] * 6 + [_f32] * 9 + [_vp] * 5
+    lib.sb200_activate.restype = _i32
+    lib.sb200_activate.argtypes = [_i32] + [_vp] * 7
+    lib.sb200_surfel_update.restype = _i32
+    lib.sb200_surfel_update.argtypes = ([_i32, _i32] + [_vp] * 3 + [_vp] * 5 + [_vp] * 7 + [_i64, _vp, _vp] +
+                                        [_f32] * 3 + [_vp])
+    if lib.sb200_abi_version() != 3:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -114,7 +123,8 @@ def _count_buffer(device):
     return buf
 
 
-STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam")
+STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam",
+          "map_loss", "activate", "update")
 
 
 def profile_enable(on=True):
@@ -343,4 +353,7 @@ class SparseGaussianAdam(torch.optim.Adam):
                    "sb200_adam_update")
 
 
-__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "SparseGaussianAdam", "rasterize_gaussians"]
+from . import mapping  # noqa: E402  (fused mapping-step blocks: N1/N2 of SURVEY.md section 8f)
+
+__all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "SparseGaussianAdam", "rasterize_gaussians",
+           "mapping"]

@@ -1,0 +1,150 @@
+"""Fused mapping-step building blocks around the rasterizer.
+
+The drop-in names (``GaussianRasterizer`` ...) keep the reference's autograd contract.  A mapper that wants the
+whole per-view iteration of ``train_once_gaussian`` (scripts/gaussian/gaussian_base.py:353-404) on the GPU
+without ~400 torch launches uses these instead:
+
+* ``activate``        raw parameters -> rasterizer inputs          (gaussian_base.py:160-166)
+* ``RasterWorkspace`` the rasterizer's forward / backward on persistent, caller-owned buffers (no autograd)
+* ``map_loss``        ``get_loss`` + ``render_raw`` post-processing + their backward (loss_utils.py:110-153)
+* ``surfel_update``   activation backward + ``add_records`` + ``weighting_grad`` + masked Adam, one kernel
+
+All of them are thin ctypes calls into ``libsurfel_b200.so``; there is no CPU path.
+"""
+import ctypes
+
+import torch
+
+from . import _check, _count_buffer, _f32c, _load, _ptr, _stream, _vp, last_counters
+
+UPDATE_LOCAL, UPDATE_DP_PRE, UPDATE_DP_POST = 0, 1, 2
+GROUP_COLS = (3, 3, 1, 2, 4)  # xyz, rgb, opacity, scaling, rotation
+
+
+def activate(opacity_raw, scaling_raw, rotation_raw, out=None):
+    """(sigmoid(opacity_raw) [P,1], exp(scaling_raw) [P,2], normalize(rotation_raw) [P,4])"""
+    lib = _load()
+    o, s, r = _f32c(opacity_raw, "opacity_raw"), _f32c(scaling_raw, "scaling_raw"), _f32c(rotation_raw, "rotation_raw")
+    P = o.shape[0]
+    if out is None:
+        out = (torch.empty_like(o), torch.empty_like(s), torch.empty_like(r))
+    _check(lib.sb200_activate(P, _ptr(o), _ptr(s), _ptr(r), _ptr(out[0]), _ptr(out[1]), _ptr(out[2]),
+                              _stream(o.device)), "sb200_activate")
+    return out
+
+
+def map_loss(color, allmap, gt_rgb, gt_depth, gt_depth_cov, w2c, cx, cy, fx, fy, weights, ws=None, out=None):
+    """Returns (loss[7], dL_dcolor[3,H,W], dL_dallmap[7,H,W]); loss[0] is the total (device tensor, no sync).
+
+    weights: dict with rgb_loss, normal_loss, alpha_loss, depth_loss, dist_loss (training_args.loss_weights).
+    (cx, cy, fx, fy): column/row principal point and focal lengths = the reference's (cv, cu, fv, fu)."""
+    lib = _load()
+    color, allmap = _f32c(color, "color"), _f32c(allmap, "allmap")
+    gt_rgb, gt_depth, gt_cov = _f32c(gt_rgb, "gt_rgb"), _f32c(gt_depth, "gt_depth"), _f32c(gt_depth_cov, "gt_depth_cov")
+    w2c = _f32c(w2c, "w2c")
+    H, W = color.shape[-2], color.shape[-1]
+    if allmap.shape != (7, H, W) or gt_rgb.shape != (3, H, W) or gt_depth.numel() != H * W or gt_cov.numel() != H * W:
+        raise RuntimeError("map_loss: shape mismatch")
+    if w2c.numel() != 16:
+        raise RuntimeError("map_loss: w2c must be a 4x4 pose")
+    dev = color.device
+    if ws is None:
+        ws = torch.empty(lib.sb200_map_loss_bytes(W, H), dtype=torch.uint8, device=dev)
+    if out is None:
+        out = (torch.empty(7, dtype=torch.float32, device=dev), torch.empty_like(color), torch.empty_like(allmap))
+    loss, d_color, d_allmap = out
+    _check(lib.sb200_map_loss(W, H, _ptr(color), _ptr(allmap), _ptr(gt_rgb), _ptr(gt_depth), _ptr(gt_cov), _ptr(w2c),
+                              float(cx), float(cy), float(fx), float(fy), float(weights["rgb_loss"]),
+                              float(weights["normal_loss"]), float(weights["alpha_loss"]),
+                              float(weights["depth_loss"]), float(weights["dist_loss"]), _ptr(ws), _ptr(loss),
+                              _ptr(d_color), _ptr(d_allmap), _stream(dev)), "sb200_map_loss")
+    return loss, d_color, d_allmap
+
+
+class RasterWorkspace:
+    """Persistent buffers for one (P, W, H): the rasterizer's forward and backward without autograd and without
+    per-call allocation.  Only the sort scratch and the sorted id list depend on the data (R); they grow
+    geometrically and are kept."""
+
+    def __init__(self, P, W, H, device):
+        lib = _load()
+        self.P, self.W, self.H, self.device = P, W, H, device
+        u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=device)
+        f = lambda *s: torch.empty(s, dtype=torch.float32, device=device)
+        self.geom = u8(lib.sb200_geom_bytes(P))
+        self.image = u8(lib.sb200_image_bytes(W, H))
+        self.grad_ws = u8(lib.sb200_grad_bytes(P))
+        self.loss_ws = u8(lib.sb200_map_loss_bytes(W, H))
+        self.binning = u8(0)
+        self.point_list = torch.empty(0, dtype=torch.int32, device=device)
+        self.color, self.allmap = f(3, H, W), f(7, H, W)
+        self.radii = torch.empty(P, dtype=torch.int32, device=device)
+        self.d_means3D, self.d_means2D, self.d_colors, self.d_opacity = f(P, 3), f(P, 3), f(P, 3), f(P, 1)
+        self.d_scales, self.d_rot, self.scores = f(P, 2), f(P, 4), f(P, 2)
+        self.loss_out = (f(7), f(3, H, W), f(7, H, W))
+        self.pixel_mask = torch.ones(H * W, dtype=torch.bool, device=device)
+        self.R = 0
+
+    def forward(self, means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix):
+        lib = _load()
+        P, W, H, dev = self.P, self.W, self.H, self.device
+        stream = _stream(dev)
+        count = _count_buffer(dev)
+        _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(opacities),
+                                       _ptr(colors), _ptr(viewmatrix), _ptr(projmatrix), _ptr(self.geom),
+                                       _ptr(self.radii), _vp(count.data_ptr()), stream), "sb200_forward_begin")
+        R = int(count[0])
+        self.R = R
+        last_counters.update(P=P, R=R, W=W, H=H)
+        need = lib.sb200_binning_bytes(R)
+        if self.binning.numel() < need:
+            self.binning = torch.empty(int(need * 1.25) + 4096, dtype=torch.uint8, device=dev)
+        if self.point_list.numel() < R:
+            self.point_list = torch.empty(int(R * 1.25) + 1024, dtype=torch.int32, device=dev)
+        _check(lib.sb200_forward_finish(P, W, H, R, _ptr(bg), _ptr(self.geom), _vp(self.binning.data_ptr()),
+                                        _vp(self.point_list.data_ptr()), _ptr(self.image), _ptr(self.color),
+                                        _ptr(self.allmap), stream), "sb200_forward_finish")
+        return self.color, self.radii, self.allmap
+
+    def backward(self, d_color, d_allmap, means3D, scales, rotations, bg, viewmatrix, projmatrix, tanfovx, tanfovy,
+                 pixel_mask=None):
+        lib = _load()
+        mask = self.pixel_mask if pixel_mask is None else pixel_mask
+        _check(lib.sb200_backward(self.P, self.W, self.H, self.R, _ptr(bg), float(tanfovx), float(tanfovy),
+                                  _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix),
+                                  _ptr(self.radii), _ptr(self.geom), _vp(self.point_list.data_ptr()), _ptr(self.image),
+                                  _ptr(self.color), _ptr(self.allmap), _ptr(d_color), _ptr(d_allmap), _ptr(mask),
+                                  _ptr(self.grad_ws), _ptr(self.d_means3D), _ptr(self.d_means2D), _ptr(self.d_colors),
+                                  _ptr(self.d_opacity), _ptr(self.d_scales), _ptr(self.d_rot), _vp(None),
+                                  _ptr(self.scores), _stream(self.device)), "sb200_backward")
+
+
+def _ptr_array(tensors):
+    arr = (ctypes.c_void_p * 5)()
+    for i, t in enumerate(tensors):
+        arr[i] = t.data_ptr()
+    return arr
+
+
+def surfel_update(mode, params, exp_avg, exp_avg_sq, lr, ws, stable_mask, local_scores, global_scores, kf_max_scores,
+                  kf_id, kf, fused=None, betas=(0.9, 0.999), eps=1e-15):
+    """One fused per-surfel pass after ``RasterWorkspace.backward`` (see include/surfel_b200.h).
+
+    params / exp_avg / exp_avg_sq: 5 contiguous CUDA tensors (xyz, rgb, opacity, scaling, rotation; raw values);
+    ws: the RasterWorkspace holding this view's gradients, scores and radii."""
+    lib = _load()
+    P = params[0].shape[0]
+    for grp in (params, exp_avg, exp_avg_sq):
+        for t, nc in zip(grp, GROUP_COLS):
+            if not (t.is_cuda and t.is_contiguous() and t.dtype == torch.float32 and t.numel() == P * nc):
+                raise RuntimeError("surfel_update needs contiguous float32 CUDA tensors of the five groups")
+    if kf_id.dtype != torch.int64:
+        raise RuntimeError("kf_id must be int64")
+    lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
+    _check(lib.sb200_surfel_update(P, int(mode), _ptr_array(params), _ptr_array(exp_avg), _ptr_array(exp_avg_sq),
+                                   _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
+                                   _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(stable_mask),
+                                   _ptr(local_scores), _ptr(global_scores), _ptr(kf_max_scores), _ptr(kf_id),
+                                   int(kf), _ptr(fused) if fused is not None else _vp(None), lr_arr,
+                                   float(betas[0]), float(betas[1]), float(eps), _stream(params[0].device)),
+           "sb200_surfel_update")

@@ -85,8 +85,14 @@ def depth_propagate_normal(depth, fx, fy, cx, cy):
 class SurfelMapper:
     """Surfel parameters + optimizer + the per-view training iteration, for a given rasterizer module."""
 
-    def __init__(self, module, scene, device, supervision="rgb+depth", world_size=1, process_group=None):
+    def __init__(self, module, scene, device, supervision="rgb+depth", world_size=1, process_group=None, fused=None):
+        """fused: run the per-view iteration through the module's fused mapping blocks (``module.mapping``:
+        activate / RasterWorkspace / map_loss / surfel_update, SURVEY.md section 8f N1+N2) instead of torch
+        autograd + torch loss.  Default: on when the module has them (the reference build has not)."""
         self.mod = module
+        self.fused = hasattr(module, "mapping") if fused is None else bool(fused)
+        if self.fused and not hasattr(module, "mapping"):
+            raise RuntimeError("fused=True needs a rasterizer module with the fused mapping blocks")
         self.device = device
         self.weights = LOSS_WEIGHTS[supervision]
         self.W, self.H = scene["W"], scene["H"]
@@ -115,6 +121,17 @@ class SurfelMapper:
         self._stable_mask = torch.zeros(P, dtype=torch.bool, device=dev)
         self._globalkf_id = torch.zeros(P, dtype=torch.long, device=dev)
         self._globalkf_max_scores = torch.zeros(P, device=dev)
+        if self.fused:
+            mp = self.mod.mapping
+            self._ws = mp.RasterWorkspace(P, self.W, self.H, dev)
+            self._act = (torch.empty(P, 1, device=dev), torch.empty(P, 2, device=dev), torch.empty(P, 4, device=dev))
+            for group in self.optimizer.param_groups:  # the state SparseGaussianAdam.step creates lazily
+                prm = group["params"][0]
+                st = self.optimizer.state[prm]
+                if len(st) == 0:
+                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                    st["exp_avg"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
+                    st["exp_avg_sq"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
         if self.world_size > 1:
             # fused gradient buffer: parameter .grad tensors are column blocks of one allocation so that a
             # single NCCL all-reduce moves gradients, scores and visibility
@@ -164,6 +181,8 @@ class SurfelMapper:
     def train_view(self, view, gt, kf_id=0):
         """render -> loss -> backward -> score bookkeeping -> weighting_grad -> masked Adam.  Returns the loss
         tensor (device).  With world_size > 1 every rank calls this with its own view of the window."""
+        if self.fused:
+            return self._train_view_fused(view, gt, kf_id)
         dp = self.world_size > 1
         if dp:
             self._fused.zero_()
@@ -194,6 +213,33 @@ class SurfelMapper:
         else:
             self.optimizer.zero_grad()
         return total_loss.detach()
+
+    @torch.no_grad()
+    def _train_view_fused(self, view, gt, kf_id):
+        """The same iteration in 20 launches of the library: activate -> rasterizer forward -> fused loss ->
+        rasterizer backward -> one per-surfel update kernel (two around the all-reduce with world_size > 1)."""
+        mp, ws = self.mod.mapping, self._ws
+        prm = [getattr(self, k).data for k in GROUPS]
+        st = [self.optimizer.state[getattr(self, k)] for k in GROUPS]
+        m, v = [x["exp_avg"] for x in st], [x["exp_avg_sq"] for x in st]
+        lr = [g["lr"] for g in self.optimizer.param_groups]
+        eps = self.optimizer.param_groups[0]["eps"]
+        opac, scales, rot = mp.activate(prm[2], prm[3], prm[4], out=self._act)
+        ws.forward(prm[0], scales, rot, opac, prm[1], self.bg, view["viewmatrix"], view["projmatrix"])
+        loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gt["rgb"], gt["depth"], gt["depth_cov"], view["w2c"],
+                                              self.cx, self.cy, self.fx, self.fy, self.weights, ws=ws.loss_ws,
+                                              out=ws.loss_out)
+        ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
+                    view["tanfovx"], view["tanfovy"])
+        book = (self._stable_mask, self._local_scores, self._global_scores, self._globalkf_max_scores, self._globalkf_id)
+        if self.world_size > 1:
+            mp.surfel_update(mp.UPDATE_DP_PRE, prm, m, v, lr, ws, *book, kf_id, fused=self._fused, eps=eps)
+            torch.distributed.all_reduce(self._fused, group=self.pg)
+            mp.surfel_update(mp.UPDATE_DP_POST, prm, m, v, lr, ws, *book, kf_id, fused=self._fused, eps=eps)
+        else:
+            mp.surfel_update(mp.UPDATE_LOCAL, prm, m, v, lr, ws, *book, kf_id, eps=eps)
+        self.last_radii = ws.radii
+        return loss[0]
 
     def _add_records(self, cur, kf_id):
         """gaussian_model.py:163-168 and gaussian_base.py:388-392"""
