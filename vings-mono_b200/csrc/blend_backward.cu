@@ -7,18 +7,54 @@
 //
 // The reference needs 12-float-per-pixel checkpoints every 32 splats (written by its forward) so that
 // one warp per bucket can start mid-tile.  Here one CTA owns a tile and walks it front to back once,
-// recomputing the forward state on the fly, so no checkpoint is ever written or read.  A thread owns
-// a pixel; for each splat the 20 per-splat gradient terms of the 32 pixels of a warp are reduced with
-// a 21-shuffle multi-value butterfly (only when some lane of the warp actually hit the splat), the 8
-// warps' partial sums meet in shared memory, and ONE global atomic per (tile, splat, term) is issued -
-// the same count as the reference's per-bucket-lane atomics, with no 23-register shuffle pipeline.
+// recomputing the forward state on the fly, so no checkpoint is ever written or read.
+//
+// Structure (round 2 of this kernel; profiles/r01_blend_backward_lines.txt showed 25 % of the stall samples
+// on the two CTA barriers per 32-surfel batch of the first version, with 59 % issue utilisation):
+//   * 8 warps (one 8x4 pixel block each, a thread owns a pixel) that never meet at a CTA barrier inside the walk;
+//   * the sorted surfels' 128-byte records are gathered with one cp.async.bulk (TMA engine, 1-D) per surfel
+//     into an 8-stage shared-memory ring of 32-surfel batches; a stage is handed to the warps by an mbarrier
+//     (expect_tx / complete_tx bytes) and handed back through a shared counter: the LAST warp to finish a
+//     batch refills its stage with the batch 8 ahead, so a warp waits only for data it needs and the warps
+//     drift up to 7 batches apart (a dedicated producer warp made 9 warps per CTA, which the four 16 K-register
+//     SM sub-partitions cannot hold twice at 112 registers: measured 1 CTA/SM and 3.0 ms);
+//   * per hit surfel a 21-shuffle multi-value butterfly reduces the 20 gradient terms over the warp's 32
+//     pixels and 20 lanes issue ONE coalesced red.global.add.f32 over the surfel's 80-byte accumulation
+//     record (3 sectors); there is no cross-warp combine and no shared accumulation buffer;
+//   * every warp stops at ITS OWN last contributor (warp max), not the tile's.
 #include "pair_math.cuh"
-#include <cuda_pipeline.h>
 
-#define BB_THREADS 256
-#define BB_WARPS 8
+#define BB_CWARPS 8
+#define BB_THREADS (BB_CWARPS * 32)
 #define BB_BATCH 32  // == the reference's bucket size; bucket boundaries are part of the semantics (Q5)
-#define BB_Q 7       // quads 0..6 of the record go to s_q, quad 7 (box) to s_bb
+#define BB_STAGES 8
+
+__device__ __forceinline__ uint32_t bb_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bb_mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bb_smem(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void bb_mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bb_smem(bar)) : "memory");
+}
+__device__ __forceinline__ void bb_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bb_smem(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bb_mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "BB_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra BB_DONE_%=;\n"
+        "bra BB_WAIT_%=;\n"
+        "BB_DONE_%=:\n"
+        "}\n" ::"r"(bb_smem(bar)), "r"(parity) : "memory");
+}
+// 1-D bulk copy global -> shared through the TMA engine; completion is signalled on `bar` in bytes
+__device__ __forceinline__ void bb_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(bb_smem(dst)), "l"(src), "r"(bytes), "r"(bb_smem(bar)) : "memory");
+}
 
 // Multi-value warp reduction: every lane holds v[0..K); afterwards lane L holds in v[0] the warp-wide
 // sum of value slot(L) (or junk if slot(L) < 0).  Each step halves the number of live values.
@@ -68,26 +104,19 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                          const float* __restrict__ out_others, const float* __restrict__ dL_dpixels,
                          const float* __restrict__ dL_dothers, const bool* __restrict__ pixel_mask,
                          float* __restrict__ grad_acc) {
-    __shared__ __align__(16) float4 s_q[2][BB_BATCH][BB_Q];
-    __shared__ __align__(16) float4 s_bb[2][BB_BATCH];
-    __shared__ uint32_t s_id[2][BB_BATCH];
-    __shared__ float s_acc[BB_WARPS][BB_BATCH][SB_GRAD_F];
-    __shared__ uint32_t s_wmask[BB_WARPS];
-    __shared__ uint32_t s_maxlast[BB_WARPS];
+    __shared__ __align__(128) float4 s_rec[BB_STAGES][BB_BATCH][SB_REC_F4];
+    __shared__ uint32_t s_id[BB_STAGES][BB_BATCH];
+    __shared__ __align__(8) uint64_t s_full[BB_STAGES];
+    __shared__ uint32_t s_done[BB_STAGES];
+    __shared__ uint32_t s_maxlast[BB_CWARPS];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t tile = blockIdx.x;
     const uint32_t tx = tile % grid_x, ty = tile / grid_x;
     // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it (as in the forward)
-#ifdef SB_DEBUG_STRIP_MAPPING
-    const uint32_t wx0 = tx * SB_TILE_X, wy0 = ty * SB_TILE_Y + wid * 2;
-    const uint32_t px = wx0 + (lane & 15), py = wy0 + (lane >> 4);
-    const float bx0 = (float)wx0, bx1 = (float)(wx0 + 15), by0 = (float)wy0, by1 = (float)(wy0 + 1);
-#else
     const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
     const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
     const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
-#endif
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
@@ -124,31 +153,40 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     }
     const float bgc[3] = {bg[0], bg[1], bg[2]};
 
-    // tile-wide max of `last` bounds the walk (reference: max_contrib bucket skip, backward.cu:503-505)
+    // tile-wide max of `last` bounds the walk (reference: max_contrib bucket skip, backward.cu:503-505);
+    // each warp blends only up to its own max
     uint32_t wmax = last;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
     if (lane == 0) s_maxlast[wid] = wmax;
+    if (tid < BB_STAGES) {
+        bb_mbar_init(&s_full[tid], 1);
+        s_done[tid] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
     __syncthreads();
     uint32_t maxlast = 0;
 #pragma unroll
-    for (int w = 0; w < BB_WARPS; w++) maxlast = max(maxlast, s_maxlast[w]);
+    for (int w = 0; w < BB_CWARPS; w++) maxlast = max(maxlast, s_maxlast[w]);
     const int n_walk = min(n, (int)maxlast);
     const int nbatches = (n_walk + BB_BATCH - 1) / BB_BATCH;
-    const bool warp_active = wmax > 0;
 
-    auto issue = [&](int b) {
+    // gather the records of batch b into ring stage b % BB_STAGES (called by one whole warp)
+    auto fill = [&](int b) {
+        const int st = b % BB_STAGES;
         const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
-        const uint32_t* ids = point_list + range.x + b * BB_BATCH;
-        if (tid < cnt * SB_REC_F4) {
-            int sp = tid >> 3, q = tid & 7;
-            uint32_t id = __ldg(ids + sp);
-            if (q == 0) s_id[b & 1][sp] = id;
-            float4* dst = (q < BB_Q) ? &s_q[b & 1][sp][q] : &s_bb[b & 1][sp];
-            __pipeline_memcpy_async(dst, rec + (size_t)id * SB_REC_F4 + q, 16);
+        uint32_t id = 0;
+        if (lane < cnt) {
+            id = __ldg(point_list + range.x + b * BB_BATCH + lane);
+            s_id[st][lane] = id;
         }
-        __pipeline_commit();
+        __syncwarp();
+        if (lane == 0) bb_mbar_expect_tx(&s_full[st], (uint32_t)cnt * (SB_REC_F4 * 16));
+        __syncwarp();
+        if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
     };
+    if (wid < BB_STAGES && wid < nbatches) fill(wid);  // BB_STAGES == BB_CWARPS: warp w primes stage w
+    const int my_batches = (min(n_walk, (int)wmax) + BB_BATCH - 1) / BB_BATCH;
 
     // running state
     float T = 1.f;              // transmittance as the backward propagates it
@@ -164,18 +202,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 
     const int slot = butterfly_slot(lane, SB_GRAD_F);
 
-    if (nbatches > 0) issue(0);
     for (int b = 0; b < nbatches; b++) {
-        if (b + 1 < nbatches) {
-            issue(b + 1);
-            __pipeline_wait_prior(1);
-        } else {
-            __pipeline_wait_prior(0);
-        }
-        __syncthreads();
+        const int st = b % BB_STAGES;
+        bb_mbar_wait(&s_full[st], (uint32_t)(b / BB_STAGES) & 1u);
         const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
-        uint32_t cmask = 0;
-        if (warp_active) {
+        if (b < my_batches) {
             // ---- bucket start: what the reference reloads from its checkpoint ----
             if (div) {
                 T = Tf;
@@ -186,11 +217,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             ar_reg = reg_f - fin_reg;
             M1b = M1;
             M2b = M2;
-            const float4(*sr)[BB_Q] = s_q[b & 1];
+            const float4(*sr)[SB_REC_F4] = s_rec[st];
             // warp-level cull: lane tests surfel `lane`'s box against the warp's 8x4 pixel block
             bool ov = false;
             if (lane < cnt) {
-                const float4 bb = s_bb[b & 1][lane];
+                const float4 bb = sr[lane][SB_REC_BBOX];
                 ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
             }
             unsigned vm = __ballot_sync(0xffffffffu, ov);
@@ -200,10 +231,6 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             while (vm) {
                 const int j = __ffs(vm) - 1;
                 vm &= vm - 1;
-                float g[SB_GRAD_F];
-#pragma unroll
-                for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
-                bool hit = false;
                 // lane-level cull (division free, surfel_math.cuh): outside the alpha >= 1/255 footprint
                 const float4 c0 = sr[j][0], c1 = sr[j][1], c2 = sr[j][2];
                 const float2 d = {c0.w - pixf.x, c1.w - pixf.y};
@@ -217,7 +244,13 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #else
                 const bool culled = E > 0.0f && (r2 + r2) > c2.w;
 #endif
-                if ((uint32_t)(b * BB_BATCH + j) < last && !culled) {
+                const bool pass = (uint32_t)(b * BB_BATCH + j) < last && !culled;
+                if (!__any_sync(0xffffffffu, pass)) continue;
+                float g[SB_GRAD_F];
+#pragma unroll
+                for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
+                bool hit = false;
+                if (pass) {
                     const float4 q0 = sr[j][SB_REC_TU], q1 = sr[j][SB_REC_TV], q2 = sr[j][SB_REC_TW];
                     const float3 Tu = {q0.x, q0.y, q0.z}, Tv = {q1.x, q1.y, q1.z}, Tw = {q2.x, q2.y, q2.z};
                     const float opa = q0.w;
@@ -346,30 +379,25 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                 }
                 if (__any_sync(0xffffffffu, hit)) {
                     Butterfly<SB_GRAD_F, 16>::run(g, lane);
-                    if (slot >= 0) s_acc[wid][j][slot] = g[0];
-                    cmask |= 1u << j;
+                    // 20 lanes, 20 consecutive floats of the surfel's accumulation record: one coalesced RED
+                    if (slot >= 0) atomicAdd(grad_acc + (size_t)s_id[st][j] * SB_GRAD_F + slot, g[0]);
                 }
             }
         }
-        if (lane == 0) s_wmask[wid] = cmask;
-        __syncthreads();
-        // ---- combine the 8 warps' partial sums; one global atomic per (splat, term) ----
-        for (int e = tid; e < cnt * SB_GRAD_F; e += BB_THREADS) {
-            int j = e / SB_GRAD_F, comp = e - j * SB_GRAD_F;
-            float sum = 0.f;
-            bool any = false;
-#pragma unroll
-            for (int w = 0; w < BB_WARPS; w++) {
-                if ((s_wmask[w] >> j) & 1u) {
-                    sum += s_acc[w][j][comp];
-                    any = true;
-                }
-            }
-            if (any) atomicAdd(grad_acc + (size_t)s_id[b & 1][j] * SB_GRAD_F + comp, sum);
+        // hand the stage back: the last of the 8 warps to get here refills it with the batch BB_STAGES ahead
+        __syncwarp();
+        uint32_t old = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            old = atomicAdd(&s_done[st], 1u);
         }
-        __syncthreads();
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == BB_CWARPS - 1) {
+            if (lane == 0) s_done[st] = 0;
+            __threadfence_block();
+            if (b + BB_STAGES < nbatches) fill(b + BB_STAGES);
+        }
     }
-    __pipeline_wait_prior(0);
 }
 
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
