@@ -27,7 +27,9 @@
 #define BB_CWARPS 8
 #define BB_THREADS (BB_CWARPS * 32)
 #define BB_BATCH 32  // == the reference's bucket size; bucket boundaries are part of the semantics (Q5)
+#ifndef BB_STAGES
 #define BB_STAGES 8
+#endif
 
 __device__ __forceinline__ uint32_t bb_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void bb_mbar_init(uint64_t* bar, uint32_t count) {
@@ -54,6 +56,13 @@ __device__ __forceinline__ void bb_mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ void bb_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(bb_smem(dst)), "l"(src), "r"(bytes), "r"(bb_smem(bar)) : "memory");
+}
+
+// Gradient-side arithmetic is not gated (only k, l, p, s, rho, G, alpha decide which pairs blend, and those stay
+// bit-pinned in pair_math.cuh), so its divisions use the MUFU reciprocal: the gradients are compared with the
+// reference at 5e-4 relative L1 (atomic-order jitter), fp32 approximate division is ~1e-7.
+__device__ __forceinline__ float bb_ndc_depth_fast(float depth) {
+    return (1.0f - SB_NEAR * __fdividef(1.0f, depth)) * (SB_FAR / (SB_FAR - SB_NEAR));
 }
 
 // Multi-value warp reduction: every lane holds v[0..K); afterwards lane L holds in v[0] the warp-wide
@@ -96,7 +105,10 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
     return n_real >= 1 ? base : -1;
 }
 
-__global__ void __launch_bounds__(BB_THREADS)
+#ifndef BB_MIN_CTAS
+#define BB_MIN_CTAS 3  // 80 registers (~100 B of spills) for 24 warps per SM: measured 7 % faster than 2 CTAs at 121
+#endif
+__global__ void __launch_bounds__(BB_THREADS, BB_MIN_CTAS)
 sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
                          const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                          const float* __restrict__ bg, const float* __restrict__ final_T,
@@ -109,6 +121,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     __shared__ __align__(8) uint64_t s_full[BB_STAGES];
     __shared__ uint32_t s_done[BB_STAGES];
     __shared__ uint32_t s_maxlast[BB_CWARPS];
+    __shared__ float s_shadow[9][BB_THREADS];  // forward-state shadow of the Q4 case: ar[8], T
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const uint32_t tile = blockIdx.x;
@@ -151,7 +164,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
         fin_reg = out_others[6 * HW + pix_id];
         // median-depth channel (5) deliberately receives no gradient (Q3)
     }
-    const float bgc[3] = {bg[0], bg[1], bg[2]};
+    // sum_ch bg[ch] * dL_dpixel[ch], accumulated in the reference's order (backward.cu:712-718); constant per pixel
+    float bg_dot_dpixel = 0.0f;
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += bg[ch] * dLc[ch];
 
     // tile-wide max of `last` bounds the walk (reference: max_contrib bucket skip, backward.cu:503-505);
     // each warp blends only up to its own max
@@ -185,7 +201,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
         __syncwarp();
         if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
     };
-    if (wid < BB_STAGES && wid < nbatches) fill(wid);  // BB_STAGES == BB_CWARPS: warp w primes stage w
+    for (int b0 = wid; b0 < BB_STAGES && b0 < nbatches; b0 += BB_CWARPS) fill(b0);  // prime the ring
     const int my_batches = (min(n_walk, (int)wmax) + BB_BATCH - 1) / BB_BATCH;
 
     // running state
@@ -197,8 +213,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     // shadow of the true forward state, live only after a forward-skipped splat was blended by the
     // backward inside the current bucket (Q4); the next bucket start snaps back to it
     bool div = false;
-    float Tf = 1.f;
-    float arf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    // (T and ar[8] of the shadow live in shared memory, s_shadow[.][tid]: touched only after a Q4 pair)
 
     const int slot = butterfly_slot(lane, SB_GRAD_F);
 
@@ -209,9 +224,9 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
         if (b < my_batches) {
             // ---- bucket start: what the reference reloads from its checkpoint ----
             if (div) {
-                T = Tf;
+                T = s_shadow[8][tid];
 #pragma unroll
-                for (int i = 0; i < 8; i++) ar[i] = arf[i];
+                for (int i = 0; i < 8; i++) ar[i] = s_shadow[i][tid];
                 div = false;
             }
             ar_reg = reg_f - fin_reg;
@@ -223,6 +238,9 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             if (lane < cnt) {
                 const float4 bb = sr[lane][SB_REC_BBOX];
                 ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+#ifdef SB_BLOCK_CULL  // opt-in: measured neutral
+                if (ov) ov = !sb_block_culled(sr[lane][0], sr[lane][1], sr[lane][2], bx0, bx1, by0, by1);
+#endif
             }
             unsigned vm = __ballot_sync(0xffffffffu, ov);
 #ifdef SB_DEBUG_NO_WARP_CULL
@@ -231,6 +249,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             while (vm) {
                 const int j = __ffs(vm) - 1;
                 vm &= vm - 1;
+                const bool live = (uint32_t)(b * BB_BATCH + j) < last;
                 // lane-level cull (division free, surfel_math.cuh): outside the alpha >= 1/255 footprint
                 const float4 c0 = sr[j][0], c1 = sr[j][1], c2 = sr[j][2];
                 const float2 d = {c0.w - pixf.x, c1.w - pixf.y};
@@ -244,7 +263,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #else
                 const bool culled = E > 0.0f && (r2 + r2) > c2.w;
 #endif
-                const bool pass = (uint32_t)(b * BB_BATCH + j) < last && !culled;
+                const bool pass = live && !culled;
                 if (!__any_sync(0xffffffffu, pass)) continue;
                 float g[SB_GRAD_F];
 #pragma unroll
@@ -292,40 +311,38 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                         // the backward's state leaves the forward's until the next bucket start
                         if (hit_b != contrib_f && !div) {
                             div = true;
-                            Tf = T;
+                            s_shadow[8][tid] = T;
 #pragma unroll
-                            for (int i = 0; i < 8; i++) arf[i] = ar[i];
+                            for (int i = 0; i < 8; i++) s_shadow[i][tid] = ar[i];
                         }
                         // ---- true forward bookkeeping (moments + distortion prefix) ----
                         if (contrib_f) {
-                            const float m_f = sb_ndc_depth(c_d_fwd);
-                            const float Tt = div ? Tf : T;
+                            const float m_f = bb_ndc_depth_fast(c_d_fwd);
+                            const float Tt = div ? s_shadow[8][tid] : T;
                             const float wf = alpha_f * Tt;
                             reg_f += (m_f * m_f * (1 - Tt) + M2 - 2 * m_f * M1) * wf;
                             M1 += m_f * wf;
                             M2 += m_f * m_f * wf;
                             if (div) {
-                                arf[0] += wf * c[0]; arf[1] += wf * c[1]; arf[2] += wf * c[2];
-                                arf[3] += wf * c_d_fwd;  arf[4] += wf;
-                                arf[5] += wf * nrm[0]; arf[6] += wf * nrm[1]; arf[7] += wf * nrm[2];
-                                Tf = Tf * (1 - alpha_f);
+                                s_shadow[0][tid] += wf * c[0]; s_shadow[1][tid] += wf * c[1]; s_shadow[2][tid] += wf * c[2];
+                                s_shadow[3][tid] += wf * c_d_fwd; s_shadow[4][tid] += wf;
+                                s_shadow[5][tid] += wf * nrm[0]; s_shadow[6][tid] += wf * nrm[1]; s_shadow[7][tid] += wf * nrm[2];
+                                s_shadow[8][tid] = Tt * (1 - alpha_f);
                             }
                         }
                         if (hit_b) {
                             hit = true;
-                            const float m_d = sb_ndc_depth(c_d);
-                            const float dmd_dd = (SB_FAR * SB_NEAR) / ((SB_FAR - SB_NEAR) * c_d * c_d);
+                            const float m_d = bb_ndc_depth_fast(c_d);
+                            const float dmd_dd = __fdividef((SB_FAR * SB_NEAR) / (SB_FAR - SB_NEAR), c_d * c_d);
                             // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
                             const float dchannel_dcolor = alpha * T;
-                            const float inv1ma = 1.0f / (1.0f - alpha);
-                            float bg_dot_dpixel = 0.0f;
+                            const float inv1ma = __fdividef(1.0f, 1.0f - alpha);  // alpha <= 0.99
                             float dL_dalpha = 0.0f;
 #pragma unroll
                             for (int ch = 0; ch < 3; ch++) {
                                 ar[ch] += T * alpha * c[ch];
                                 g[15 + ch] = dchannel_dcolor * dLc[ch];
                                 dL_dalpha += ((c[ch] * T) - inv1ma * (-ar[ch])) * dLc[ch];
-                                bg_dot_dpixel += bgc[ch] * dLc[ch];
                                 g[19] += fabsf(dchannel_dcolor * dLc[ch]);
                             }
                             dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
@@ -354,8 +371,9 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                             const float dL_dG = opa * dL_dalpha;
                             if (rho3d <= rho2d) {
                                 const float2 dL_ds = {dL_dG * -G * s.x + dL_dz * Tw.x, dL_dG * -G * s.y + dL_dz * Tw.y};
-                                const float dsx_pz = dL_ds.x / p.z;
-                                const float dsy_pz = dL_ds.y / p.z;
+                                const float inv_pz = __fdividef(1.0f, p.z);
+                                const float dsx_pz = dL_ds.x * inv_pz;
+                                const float dsy_pz = dL_ds.y * inv_pz;
                                 const float3 dL_dp = {dsx_pz, dsy_pz, -(dsx_pz * s.x + dsy_pz * s.y)};
                                 const float3 dL_dk = {l.y * dL_dp.z - l.z * dL_dp.y, l.z * dL_dp.x - l.x * dL_dp.z,
                                                       l.x * dL_dp.y - l.y * dL_dp.x};

@@ -87,6 +87,9 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
             if (c + lane < cnt) {
                 const float4 bb = sbb[c + lane];
                 ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+#ifdef SB_BLOCK_CULL  // opt-in: measured neutral
+                if (ov) ov = !sb_block_culled(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bx0, bx1, by0, by1);
+#endif
             }
             unsigned m = __ballot_sync(0xffffffffu, ov);
             while (m) {

@@ -58,3 +58,59 @@ __device__ __forceinline__ float sb_pair_depth(const SbPair& g, float rho2d, flo
 __device__ __forceinline__ float sb_ndc_depth(float depth) {
     return __fmul_rn(__fadd_rn(__fdiv_rn(-SB_NEAR, depth), 1.0f), SB_FAR / (SB_FAR - SB_NEAR));
 }
+
+// ---- warp-level cull: can a whole pixel block skip a surfel? ----
+// The lane-level test of the blend kernels rejects pixel (px,py) iff  E(d) > 0  &&  2|d|^2 > tau  with
+// d = xy - pixel and E(d) = q.x^2 + q.y^2 - tau q.z^2, q = C + A d.x + B d.y (record quads 0-2).  One lane
+// evaluates this for ONE surfel against the warp's whole block [bx0,bx1] x [by0,by1] (pixel centres, inclusive):
+// the block is skipped when the minimum of E over the rectangle is positive (E is a quadratic form; when it is
+// an ellipse -- positive definite -- its minimum over a rectangle is at the stationary point if that is inside,
+// else on one of the four edges, each a clamped 1-D parabola) and the rectangle's nearest point to the centre
+// is outside the low-pass disc.  Hyperbolic forms (surfels crossing the camera plane) are never skipped here.
+// The margin covers fp32 rounding of both evaluations (expanded coefficients here, factored form per pixel):
+// every error term is bounded by eps * S with S the sum of the magnitudes of the terms of E.
+__device__ __forceinline__ bool sb_block_culled(float4 c0, float4 c1, float4 c2, float bx0, float bx1, float by0,
+                                                float by1) {
+    const float tau = c2.w;
+    const float xl = c0.w - bx1, xh = c0.w - bx0, yl = c1.w - by1, yh = c1.w - by0;  // range of d over the block
+    const float nx = fmaxf(xl, fminf(0.0f, xh)), ny = fmaxf(yl, fminf(0.0f, yh));
+    const float r2 = nx * nx + ny * ny;
+    if (!((r2 + r2) > tau * 1.0001f + 1e-4f)) return false;  // the low-pass disc reaches the block
+    const float a = c0.x * c0.x + c0.y * c0.y - tau * c0.z * c0.z;
+    const float c = c1.x * c1.x + c1.y * c1.y - tau * c1.z * c1.z;
+    const float b = 2.0f * (c0.x * c1.x + c0.y * c1.y - tau * c0.z * c1.z);
+    const float d = 2.0f * (c2.x * c0.x + c2.y * c0.y - tau * c2.z * c0.z);
+    const float e = 2.0f * (c2.x * c1.x + c2.y * c1.y - tau * c2.z * c1.z);
+    const float f = c2.x * c2.x + c2.y * c2.y - tau * c2.z * c2.z;
+    const float det = 4.0f * a * c - b * b;
+    if (!(a > 0.0f && c > 0.0f && det > 0.0f)) return false;  // not an ellipse (or NaN): visit
+    const float X = fmaxf(fabsf(xl), fabsf(xh)), Y = fmaxf(fabsf(yl), fabsf(yh));
+    const float sx_ = fabsf(c2.x) + fabsf(c0.x) * X + fabsf(c1.x) * Y;
+    const float sy_ = fabsf(c2.y) + fabsf(c0.y) * X + fabsf(c1.y) * Y;
+    const float sz_ = fabsf(c2.z) + fabsf(c0.z) * X + fabsf(c1.z) * Y;
+    const float margin = 1e-4f * (sx_ * sx_ + sy_ * sy_ + tau * sz_ * sz_);
+    // vertical edges dx = X0: g(dy) = c dy^2 + (b X0 + e) dy + (a X0^2 + d X0 + f)
+    const float ic = -0.5f / c, ia = -0.5f / a;
+    float m;
+    {
+        const float l1 = b * xl + e, k1 = (a * xl + d) * xl + f;
+        const float t1 = fminf(fmaxf(l1 * ic, yl), yh);
+        m = (c * t1 + l1) * t1 + k1;
+        const float l2 = b * xh + e, k2 = (a * xh + d) * xh + f;
+        const float t2 = fminf(fmaxf(l2 * ic, yl), yh);
+        m = fminf(m, (c * t2 + l2) * t2 + k2);
+    }
+    // horizontal edges dy = Y0: h(dx) = a dx^2 + (b Y0 + d) dx + (c Y0^2 + e Y0 + f)
+    {
+        const float l1 = b * yl + d, k1 = (c * yl + e) * yl + f;
+        const float t1 = fminf(fmaxf(l1 * ia, xl), xh);
+        m = fminf(m, (a * t1 + l1) * t1 + k1);
+        const float l2 = b * yh + d, k2 = (c * yh + e) * yh + f;
+        const float t2 = fminf(fmaxf(l2 * ia, xl), xh);
+        m = fminf(m, (a * t2 + l2) * t2 + k2);
+    }
+    // stationary point
+    const float sx = (b * e - 2.0f * c * d) / det, sy = (b * d - 2.0f * a * e) / det;
+    if (sx >= xl && sx <= xh && sy >= yl && sy <= yh) return false;  // the ellipse's centre is inside the block
+    return m > margin;
+}

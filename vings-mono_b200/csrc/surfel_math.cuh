@@ -247,3 +247,4 @@ __device__ __forceinline__ SbCull sb_cull_data(float3 Tu, float3 Tv, float3 Tw, 
     if (!(c.bbox.x <= c.bbox.y) || !(c.bbox.z <= c.bbox.w)) c.bbox = make_float4(-BIG, BIG, -BIG, BIG);
     return c;
 }
+
