@@ -199,3 +199,40 @@ def test_fused_view_matches_torch_view(sup):
     st = a._stable_mask
     assert torch.equal(b._xyz.data[st], init["_xyz"][st])
     assert not torch.equal(b._xyz.data[~st], init["_xyz"][~st])
+
+
+@pytest.mark.gpu
+def test_update_dp_modes_equal_local_on_one_rank():
+    """SB200_UPDATE_DP_PRE + (an all-reduce over one rank = identity) + SB200_UPDATE_DP_POST is the LOCAL pass on
+    the same backward outputs: same weighting, same bookkeeping, same Adam -- bit for bit.  (Two separate
+    backward passes would differ by atomic-order jitter, so the rasterizer runs once.)"""
+    mine = util.load_mine()
+    mp = mine.mapping
+    scene, views = synthetic.make_scene("C3", P=20000, W=160, H=96)
+    dev = torch.device("cuda")
+    m = mapper_step.SurfelMapper(mine, scene, dev, supervision="rgb+depth+normal+dist", fused=True)
+    for i in range(2):  # leaves non-trivial moments, scores and one view's gradients in m._ws
+        v = views[-1 - i]
+        m.train_view(mapper_step.view_to_device(v, dev), {k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()},
+                     kf_id=i + 1)
+    g = torch.Generator(device="cpu").manual_seed(4)
+    stable = (torch.rand(m.P, generator=g) < 0.1).cuda()
+
+    def state():
+        prm = [getattr(m, k).data.clone() for k in mapper_step.GROUPS]
+        st = [m.optimizer.state[getattr(m, k)] for k in mapper_step.GROUPS]
+        return (prm, [x["exp_avg"].clone() for x in st], [x["exp_avg_sq"].clone() for x in st],
+                [m._local_scores.clone(), m._global_scores.clone(), m._globalkf_max_scores.clone(), m._globalkf_id.clone()])
+
+    lr = [mapper_step.LR[k] for k in mapper_step.GROUPS]
+    pa, ma, va, ba = state()
+    mp.surfel_update(mp.UPDATE_LOCAL, pa, ma, va, lr, m._ws, stable, *ba, 7)
+    pb, mb, vb, bb = state()
+    fused = torch.zeros(16 * m.P, device=dev)
+    mp.surfel_update(mp.UPDATE_DP_PRE, pb, mb, vb, lr, m._ws, stable, *bb, 7, fused=fused)
+    assert all(torch.equal(x, y) for x, y in zip(pb + bb, state()[0] + state()[3]))  # PRE only fills the buffer
+    assert torch.equal(fused[15 * m.P:] > 0, m._ws.radii > 0)
+    mp.surfel_update(mp.UPDATE_DP_POST, pb, mb, vb, lr, m._ws, stable, *bb, 7, fused=fused)
+    for x, y in zip(pa + ma + va + ba, pb + mb + vb + bb):
+        assert torch.equal(x, y)
+    assert not torch.equal(pa[0], m._xyz.data)

@@ -170,7 +170,8 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
     }
     {
         StageScope sc(SB200_STAGE_RANGES, s);
-        rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges), s);
+        rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges),
+                                   (uint32_t*)((char*)image_ws + IL.order), s);
     }
     if (rc) return rc;
     // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does

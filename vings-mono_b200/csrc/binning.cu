@@ -95,11 +95,59 @@ int sb_launch_duplicate(int P, int W, int H, const char* geom, uint64_t* keys, u
     return 0;
 }
 
-int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, cudaStream_t s) {
+// Longest-list-first launch order of the tiles for the two blend kernels: a CTA's run time is proportional to its
+// tile's list length, lists differ by 100x across an image, and blockIdx order is dispatch order, so the long
+// tiles start first and the short ones fill the tail (LPT scheduling).  One CTA: max, 1024-bin counting sort by
+// scaled length (order inside a bin is arbitrary), scatter.
+#define ORD_THREADS 1024
+__global__ void __launch_bounds__(ORD_THREADS) sb_tile_order_kernel(int tiles, const uint2* __restrict__ ranges,
+                                                                     uint32_t* __restrict__ order) {
+    __shared__ uint32_t s_bin[ORD_THREADS];
+    __shared__ uint32_t s_max;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_max = 0;
+    s_bin[tid] = 0;
+    __syncthreads();
+    uint32_t mx = 0;
+    for (int t = tid; t < tiles; t += ORD_THREADS) mx = max(mx, ranges[t].y - ranges[t].x);
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((tid & 31) == 0 && mx) atomicMax(&s_max, mx);
+    __syncthreads();
+    const uint64_t top = s_max ? s_max : 1;
+    // bin 0 = longest
+    for (int t = tid; t < tiles; t += ORD_THREADS) {
+        const uint32_t n = ranges[t].y - ranges[t].x;
+        atomicAdd(&s_bin[(ORD_THREADS - 1) - (uint32_t)(((uint64_t)n * (ORD_THREADS - 1)) / top)], 1u);
+    }
+    __syncthreads();
+    // exclusive scan of the 1024 bins (Hillis-Steele over a copy in registers)
+    uint32_t v = s_bin[tid];
+    const uint32_t own = v;
+    for (int o = 1; o < ORD_THREADS; o <<= 1) {
+        const uint32_t add = tid >= o ? s_bin[tid - o] : 0;
+        __syncthreads();
+        v += add;
+        s_bin[tid] = v;
+        __syncthreads();
+    }
+    s_bin[tid] = v - own;
+    __syncthreads();
+    for (int t = tid; t < tiles; t += ORD_THREADS) {
+        const uint32_t n = ranges[t].y - ranges[t].x;
+        const uint32_t pos = atomicAdd(&s_bin[(ORD_THREADS - 1) - (uint32_t)(((uint64_t)n * (ORD_THREADS - 1)) / top)], 1u);
+        order[pos] = (uint32_t)t;
+    }
+}
+
+int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, uint32_t* order,
+                          cudaStream_t s) {
     SB_CUDA_CHECK(cudaMemsetAsync(ranges, 0, (size_t)tiles * sizeof(uint2), s));
-    if (R == 0) return 0;
-    int64_t nblocks = (R + 255) / 256;
-    sb_tile_ranges_kernel<<<(unsigned)nblocks, 256, 0, s>>>(R, keys_sorted, ranges);
+    if (R > 0) {
+        int64_t nblocks = (R + 255) / 256;
+        sb_tile_ranges_kernel<<<(unsigned)nblocks, 256, 0, s>>>(R, keys_sorted, ranges);
+        sb_count_launch(1);
+    }
+    sb_tile_order_kernel<<<1, ORD_THREADS, 0, s>>>(tiles, ranges, order);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -109,7 +109,7 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
 #define BB_MIN_CTAS 3  // 80 registers (~100 B of spills) for 24 warps per SM: measured 7 % faster than 2 CTAs at 121
 #endif
 __global__ void __launch_bounds__(BB_THREADS, BB_MIN_CTAS)
-sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                          const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                          const float* __restrict__ bg, const float* __restrict__ final_T,
                          const uint32_t* __restrict__ n_contrib, const float* __restrict__ out_color,
@@ -124,7 +124,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     __shared__ float s_shadow[9][BB_THREADS];  // forward-state shadow of the Q4 case: ar[8], T
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+#ifdef SB_DEBUG_NO_LPT
     const uint32_t tile = blockIdx.x;
+#else
+    const uint32_t tile = tile_order[blockIdx.x];  // longest lists first (binning.cu)
+#endif
     const uint32_t tx = tile % grid_x, ty = tile / grid_x;
     // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it (as in the forward)
     const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
@@ -246,11 +250,46 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #ifdef SB_DEBUG_NO_WARP_CULL
             vm = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
 #endif
+#ifndef SB_ONE_PHASE
+            // ---- phase 1: lane-level cull of every surviving surfel -> one pass bit per (lane, surfel) ----
+            // (division free, surfel_math.cuh: outside the alpha >= 1/255 footprint).  No vote and no branch
+            // depends on the arithmetic, and two surfels are evaluated per trip, so the LDS -> FFMA chains of
+            // neighbouring surfels overlap instead of serialising behind a per-surfel vote + branch.
+            uint32_t pm = 0;
+            while (vm) {
+                const int j0 = __ffs(vm) - 1;
+                vm &= vm - 1;
+                const int j1 = vm ? __ffs(vm) - 1 : j0;
+                vm &= vm - 1;  // (0 & anything stays 0)
+                const float4 a0 = sr[j0][0], a1 = sr[j0][1], a2 = sr[j0][2];
+                const float4 e0 = sr[j1][0], e1 = sr[j1][1], e2 = sr[j1][2];
+                const float dx0 = a0.w - pixf.x, dy0 = a1.w - pixf.y, dx1 = e0.w - pixf.x, dy1 = e1.w - pixf.y;
+                const float r0 = dx0 * dx0 + dy0 * dy0, r1 = dx1 * dx1 + dy1 * dy1;
+                const float qx0 = a2.x + a0.x * dx0 + a1.x * dy0, qx1 = e2.x + e0.x * dx1 + e1.x * dy1;
+                const float qy0 = a2.y + a0.y * dx0 + a1.y * dy0, qy1 = e2.y + e0.y * dx1 + e1.y * dy1;
+                const float qz0 = a2.z + a0.z * dx0 + a1.z * dy0, qz1 = e2.z + e0.z * dx1 + e1.z * dy1;
+                const float E0 = (qx0 * qx0 + qy0 * qy0) - a2.w * (qz0 * qz0);
+                const float E1 = (qx1 * qx1 + qy1 * qy1) - e2.w * (qz1 * qz1);
+                const bool p0 = !(E0 > 0.0f && (r0 + r0) > a2.w) && (uint32_t)(b * BB_BATCH + j0) < last;
+                const bool p1 = !(E1 > 0.0f && (r1 + r1) > e2.w) && (uint32_t)(b * BB_BATCH + j1) < last;
+                pm |= ((uint32_t)p0 << j0) | ((uint32_t)p1 << j1);
+            }
+            // ---- phase 2: the reference arithmetic, only for surfels some lane of the warp passes ----
+            uint32_t am = __reduce_or_sync(0xffffffffu, pm);
+#ifdef SB_DEBUG_NO_HEAVY
+            if (pm == 0xdeadbeefu) T += 1.f;
+            am = 0;
+#endif
+            while (am) {
+                const int j = __ffs(am) - 1;
+                am &= am - 1;
+                const bool pass = (pm >> j) & 1u;
+                const float2 d = {sr[j][0].w - pixf.x, sr[j][1].w - pixf.y};
+#else
             while (vm) {
                 const int j = __ffs(vm) - 1;
                 vm &= vm - 1;
                 const bool live = (uint32_t)(b * BB_BATCH + j) < last;
-                // lane-level cull (division free, surfel_math.cuh): outside the alpha >= 1/255 footprint
                 const float4 c0 = sr[j][0], c1 = sr[j][1], c2 = sr[j][2];
                 const float2 d = {c0.w - pixf.x, c1.w - pixf.y};
                 const float r2 = d.x * d.x + d.y * d.y;
@@ -258,13 +297,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                 const float qy = c2.y + c0.y * d.x + c1.y * d.y;
                 const float qz = c2.z + c0.z * d.x + c1.z * d.y;
                 const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
-#ifdef SB_DEBUG_NO_LANE_CULL
-                const bool culled = false;
-#else
                 const bool culled = E > 0.0f && (r2 + r2) > c2.w;
-#endif
                 const bool pass = live && !culled;
                 if (!__any_sync(0xffffffffu, pass)) continue;
+#endif
                 float g[SB_GRAD_F];
 #pragma unroll
                 for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
@@ -395,10 +431,19 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                         }
                     }
                 }
+#ifdef SB_DEBUG_NO_REDUCE
+                if (g[3] == 123.456f && g[17] == 1.0f && g[9] + g[19] + g[0] + g[14] + g[11] == 5.f) atomicAdd(grad_acc, g[1] + g[2] + g[4] + g[5] + g[6] + g[7] + g[8] + g[10] + g[12] + g[13] + g[15] + g[16] + g[18]);
+                hit = false;
+#endif
                 if (__any_sync(0xffffffffu, hit)) {
                     Butterfly<SB_GRAD_F, 16>::run(g, lane);
                     // 20 lanes, 20 consecutive floats of the surfel's accumulation record: one coalesced RED
-                    if (slot >= 0) atomicAdd(grad_acc + (size_t)s_id[st][j] * SB_GRAD_F + slot, g[0]);
+#ifdef SB_DEBUG_NO_ATOMIC
+                    if (slot >= 0 && g[0] == 123.456f)
+#else
+                    if (slot >= 0)
+#endif
+                        atomicAdd(grad_acc + (size_t)s_id[st][j] * SB_GRAD_F + slot, g[0]);
                 }
             }
         }
@@ -425,7 +470,7 @@ int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, co
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
     sb_blend_backward_kernel<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
-        W, H, grid_x, (const uint2*)(image + IL.ranges), point_list, (const float4*)geom, bg,
+        W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
         dL_dcolor, dL_dothers, pixel_mask, grad_acc);
     sb_count_launch(1);

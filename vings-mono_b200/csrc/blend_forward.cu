@@ -25,7 +25,7 @@
 #define FB_Q 7  // quads 0..6 of the record go to s_q, quad 7 (box) to s_bb
 
 __global__ void __launch_bounds__(FB_THREADS)
-sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges,
+sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                         const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                         float* __restrict__ out_color, float* __restrict__ out_others) {
@@ -33,7 +33,11 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     __shared__ __align__(16) float4 s_bb[2][FB_BATCH];
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+#ifdef SB_DEBUG_NO_LPT
     const uint32_t tile = blockIdx.x;
+#else
+    const uint32_t tile = tile_order[blockIdx.x];  // longest lists first (binning.cu)
+#endif
     const uint32_t tx = tile % grid_x, ty = tile / grid_x;
     // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it
     const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
@@ -92,6 +96,39 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
 #endif
             }
             unsigned m = __ballot_sync(0xffffffffu, ov);
+#ifndef SB_ONE_PHASE
+            // ---- phase 1: lane-level cull (division free) of every surviving surfel -> one pass bit per
+            // (lane, surfel); two surfels per trip and no vote / branch on the arithmetic, so the LDS -> FFMA
+            // chains overlap ----
+            uint32_t pm = 0;
+            while (m) {
+                const int j0 = c + __ffs(m) - 1;
+                m &= m - 1;
+                const int j1 = m ? c + __ffs(m) - 1 : j0;
+                m &= m - 1;
+                const float4 a0 = sq[j0][0], a1 = sq[j0][1], a2 = sq[j0][2];
+                const float4 e0 = sq[j1][0], e1 = sq[j1][1], e2 = sq[j1][2];
+                const float dx0 = a0.w - pixf.x, dy0 = a1.w - pixf.y, dx1 = e0.w - pixf.x, dy1 = e1.w - pixf.y;
+                const float r0 = dx0 * dx0 + dy0 * dy0, r1 = dx1 * dx1 + dy1 * dy1;
+                const float qx0 = a2.x + a0.x * dx0 + a1.x * dy0, qx1 = e2.x + e0.x * dx1 + e1.x * dy1;
+                const float qy0 = a2.y + a0.y * dx0 + a1.y * dy0, qy1 = e2.y + e0.y * dx1 + e1.y * dy1;
+                const float qz0 = a2.z + a0.z * dx0 + a1.z * dy0, qz1 = e2.z + e0.z * dx1 + e1.z * dy1;
+                const float E0 = (qx0 * qx0 + qy0 * qy0) - a2.w * (qz0 * qz0);
+                const float E1 = (qx1 * qx1 + qy1 * qy1) - e2.w * (qz1 * qz1);
+                const bool p0 = !(E0 > 0.0f && (r0 + r0) > a2.w);
+                const bool p1 = !(E1 > 0.0f && (r1 + r1) > e2.w);
+                pm |= ((uint32_t)p0 << (j0 - c)) | ((uint32_t)p1 << (j1 - c));
+            }
+            if (done) pm = 0;
+            // ---- phase 2: surfels some live lane of the warp passes ----
+            uint32_t am = __reduce_or_sync(0xffffffffu, pm);
+            while (am) {
+                const int jj = __ffs(am) - 1;
+                const int j = c + jj;
+                am &= am - 1;
+                if (done || !((pm >> jj) & 1u)) continue;
+                const float2 d = {sq[j][0].w - pixf.x, sq[j][1].w - pixf.y};  // == the reference's d (forward.cu:413)
+#else
             while (m) {
                 const int j = c + __ffs(m) - 1;
                 m &= m - 1;
@@ -104,6 +141,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
                 const float qz = c2.z + c0.z * d.x + c1.z * d.y;
                 const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
                 if (done || (E > 0.0f && (r2 + r2) > c2.w)) continue;
+#endif
                 // ---- the reference's arithmetic (forward.cu:401-468) ----
                 const float4 q3 = sq[j][SB_REC_TU], q4 = sq[j][SB_REC_TV], q5 = sq[j][SB_REC_TW];
                 const float3 Tu = {q3.x, q3.y, q3.z}, Tv = {q4.x, q4.y, q4.z}, Tw = {q5.x, q5.y, q5.z};
@@ -178,7 +216,7 @@ int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, con
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
     // geom layout: the record array is first and its offset does not depend on P
     sb_blend_forward_kernel<<<grid_x * grid_y, FB_THREADS, 0, s>>>(
-        W, H, grid_x, (const uint2*)(image + IL.ranges), point_list, (const float4*)geom, bg,
+        W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (float*)(image + IL.final_T), (uint32_t*)(image + IL.n_contrib), out_color, out_others);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());

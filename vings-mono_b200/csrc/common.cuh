@@ -74,6 +74,7 @@ struct SbImageLayout {
     size_t ranges;    // uint2[tiles]
     size_t final_T;   // float[3*HW]   T, M1, M2   (reference: ImageState::accum_alpha)
     size_t n_contrib; // uint32[2*HW]  last contributor, median contributor
+    size_t order;     // uint32[tiles] launch order of the tiles, longest list first
     size_t total;
 };
 
@@ -85,6 +86,7 @@ static inline __host__ SbImageLayout sb_image_layout(int W, int H) {
     L.ranges = o;    o = sb_align(o + tiles * 8);
     L.final_T = o;   o = sb_align(o + hw * 12);
     L.n_contrib = o; o = sb_align(o + hw * 8);
+    L.order = o;     o = sb_align(o + tiles * 4);
     L.total = o;
     return L;
 }
@@ -166,7 +168,8 @@ int sb_launch_duplicate(int P, int W, int H, const char* geom, uint64_t* keys, u
 int sb_launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_tmp, uint32_t* vals_tmp,
                          uint64_t** keys_sorted, uint32_t* vals_final, int64_t n, int end_bit, char* bin_base,
                          const SbBinLayout& L, cudaStream_t s);
-int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, cudaStream_t s);
+int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, uint32_t* order,
+                          cudaStream_t s);
 int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                             char* image, float* out_color, float* out_others, cudaStream_t s);
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
