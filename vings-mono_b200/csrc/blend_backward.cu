@@ -219,7 +219,8 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     bool div = false;
     // (T and ar[8] of the shadow live in shared memory, s_shadow[.][tid]: touched only after a Q4 pair)
 
-    const int slot = butterfly_slot(lane, SB_GRAD_F);
+    int slot = butterfly_slot(lane, SB_GRAD_F);
+    asm volatile("" : "+r"(slot));  // keep it in a register: ptxas otherwise recomputes the 5-step chain per hit (4 % of all instructions)
 
     for (int b = 0; b < nbatches; b++) {
         const int st = b % BB_STAGES;
@@ -351,9 +352,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #pragma unroll
                             for (int i = 0; i < 8; i++) s_shadow[i][tid] = ar[i];
                         }
+                        const float m_d = bb_ndc_depth_fast(c_d);
                         // ---- true forward bookkeeping (moments + distortion prefix) ----
                         if (contrib_f) {
-                            const float m_f = bb_ndc_depth_fast(c_d_fwd);
+                            const float m_f = (c_d_fwd == c_d) ? m_d : bb_ndc_depth_fast(c_d_fwd);
                             const float Tt = div ? s_shadow[8][tid] : T;
                             const float wf = alpha_f * Tt;
                             reg_f += (m_f * m_f * (1 - Tt) + M2 - 2 * m_f * M1) * wf;
@@ -368,7 +370,6 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                         }
                         if (hit_b) {
                             hit = true;
-                            const float m_d = bb_ndc_depth_fast(c_d);
                             const float dmd_dd = __fdividef((SB_FAR * SB_NEAR) / (SB_FAR - SB_NEAR), c_d * c_d);
                             // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
                             const float dchannel_dcolor = alpha * T;

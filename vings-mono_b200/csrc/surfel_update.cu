@@ -63,44 +63,76 @@ struct SbUpdateArgs {
     int P, mode;
 };
 
-static const int GRP_COLS[5] = {3, 3, 1, 2, 4};
-__constant__ int c_grp_off[5] = {0, 3, 6, 7, 9};  // column offsets of the groups inside the fused buffer
+
+// column c of the 13 raw-parameter columns -> (group, columns of the group, column inside the group)
+#define SB_GRP(c) ((c) < 3 ? 0 : (c) < 6 ? 1 : (c) < 7 ? 2 : (c) < 9 ? 3 : 4)
+#define SB_GRP_NC(g) ((g) == 0 ? 3 : (g) == 1 ? 3 : (g) == 2 ? 1 : (g) == 3 ? 2 : 4)
+#define SB_GRP_C0(g) ((g) == 0 ? 0 : (g) == 1 ? 3 : (g) == 2 ? 6 : (g) == 3 ? 7 : 9)
 
 __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int P = a.P;
     if (i >= P) return;
-    const size_t Pz = (size_t)P;
-    float g[13];
+    const size_t Pz = (size_t)P, iz = (size_t)i;
+    const int mode = a.mode;
+
+    // ---- round trip 1 (5 bytes): is this surfel updated at all? ----
+    bool visible = mode == SB200_UPDATE_DP_POST ? a.fused[15 * Pz + iz] > 0.0f : a.radii[i] > 0;
+    const bool adam = mode != SB200_UPDATE_DP_PRE && visible && !a.stable[i];
+
+    // ---- round trip 2: every other load of the pass is issued before the first store (the pointers may alias
+    // as far as the compiler knows, so loads never move above a store on their own; a load-update-store loop per
+    // scalar was 0.20 ms at 1.1 TB/s, loads-then-stores per phase 0.17 ms) ----
+    float g[13], pv[13], mv[13], vv[13];
     float cur0, cur1;
-    bool visible;
-    if (a.mode == SB200_UPDATE_DP_POST) {
-        // reduced gradients, score sums and visibility counts come back in the fused buffer
+    if (mode == SB200_UPDATE_DP_POST) {
 #pragma unroll
-        for (int grp = 0, c = 0; grp < 5; grp++) {
-            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
-            const float* blk = a.fused + (size_t)c_grp_off[grp] * Pz;
-            for (int k = 0; k < nc; k++, c++) g[c] = blk[(size_t)i * nc + k];
+        for (int c = 0; c < 13; c++) {
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            g[c] = a.fused[(size_t)SB_GRP_C0(grp) * Pz + iz * nc + (c - SB_GRP_C0(grp))];
         }
-        cur0 = a.fused[13 * Pz + 2 * (size_t)i];
-        cur1 = a.fused[13 * Pz + 2 * (size_t)i + 1];
-        visible = a.fused[15 * Pz + i] > 0.0f;
+        cur0 = a.fused[13 * Pz + 2 * iz];
+        cur1 = a.fused[13 * Pz + 2 * iz + 1];
     } else {
-        cur0 = a.cur_scores[2 * (size_t)i];
-        cur1 = a.cur_scores[2 * (size_t)i + 1];
-        visible = a.radii[i] > 0;
-        // ---- backward of the activations ----
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            g[k] = a.d_means3D[3 * (size_t)i + k];
-            g[3 + k] = a.d_colors[3 * (size_t)i + k];
+            g[k] = a.d_means3D[3 * iz + k];
+            g[3 + k] = a.d_colors[3 * iz + k];
         }
-        const float y = 1.0f / (1.0f + expf(-a.param[2][i]));
-        g[6] = a.d_opacity[i] * (1.0f - y) * y;
-        g[7] = a.d_scales[2 * (size_t)i] * expf(a.param[3][2 * (size_t)i]);
-        g[8] = a.d_scales[2 * (size_t)i + 1] * expf(a.param[3][2 * (size_t)i + 1]);
-        const float4 q = ((const float4*)a.param[4])[i];
+        g[6] = a.d_opacity[i];
+        g[7] = a.d_scales[2 * iz];
+        g[8] = a.d_scales[2 * iz + 1];
         const float4 dq = ((const float4*)a.d_rot)[i];
+        g[9] = dq.x; g[10] = dq.y; g[11] = dq.z; g[12] = dq.w;
+        cur0 = a.cur_scores[2 * iz];
+        cur1 = a.cur_scores[2 * iz + 1];
+    }
+    float glob0 = a.global_scores[2 * iz], glob1 = 0.f, loc0 = 0.f, loc1 = 0.f, kfm = 0.f;
+    if (mode != SB200_UPDATE_DP_PRE) {
+        glob1 = a.global_scores[2 * iz + 1];
+        loc0 = a.local_scores[2 * iz];
+        loc1 = a.local_scores[2 * iz + 1];
+        kfm = a.kf_max[i];
+    }
+    // raw opacity / scaling / rotation feed the activation backward of every surfel; the rest is Adam state
+    const bool need_raw = mode != SB200_UPDATE_DP_POST;
+#pragma unroll
+    for (int c = 0; c < 13; c++) {
+        const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+        const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+        pv[c] = (adam || (need_raw && c >= 6)) ? a.param[grp][e] : 0.f;
+        mv[c] = adam ? a.m[grp][e] : 0.f;
+        vv[c] = adam ? a.v[grp][e] : 0.f;
+    }
+
+    if (mode != SB200_UPDATE_DP_POST) {
+        // ---- backward of the activations (sigmoid, exp, normalize) ----
+        const float y = 1.0f / (1.0f + expf(-pv[6]));
+        g[6] = g[6] * (1.0f - y) * y;
+        g[7] = g[7] * expf(pv[7]);
+        g[8] = g[8] * expf(pv[8]);
+        const float4 q = make_float4(pv[9], pv[10], pv[11], pv[12]);
+        const float4 dq = make_float4(g[9], g[10], g[11], g[12]);
         const float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
         if (len > 1e-12f) {
             const float4 r = make_float4(q.x / len, q.y / len, q.z / len, q.w / len);
@@ -112,81 +144,55 @@ __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
         }
     }
 
-    // ---- add_records ----
-    float glob0 = a.global_scores[2 * (size_t)i];
-    if (a.mode != SB200_UPDATE_DP_PRE) {
-        a.local_scores[2 * (size_t)i] += cur0;
-        const float l1 = a.local_scores[2 * (size_t)i + 1];
-        if (cur1 > l1) a.local_scores[2 * (size_t)i + 1] = cur1;
-        glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);
-        a.global_scores[2 * (size_t)i] = glob0;
-        a.global_scores[2 * (size_t)i + 1] = fminf(fmaxf(a.global_scores[2 * (size_t)i + 1], 0.0f), 1e4f);
-        if (a.kf_max[i] < cur0) {
+    // ---- add_records (gaussian_model.py:163-168, gaussian_base.py:388-392) ----
+    glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);  // DP_PRE: this view's score counted, nothing stored yet
+    if (mode != SB200_UPDATE_DP_PRE) {
+        a.local_scores[2 * iz] = loc0 + cur0;
+        if (cur1 > loc1) a.local_scores[2 * iz + 1] = cur1;
+        a.global_scores[2 * iz] = glob0;
+        a.global_scores[2 * iz + 1] = fminf(fmaxf(glob1, 0.0f), 1e4f);
+        if (kfm < cur0) {
             a.kf_max[i] = cur0;
             a.kf_id[i] = a.kf;
         }
-    } else {
-        glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);  // this view's score counted, nothing stored yet
     }
 
-    // ---- weighting_grad ----
-    if (a.mode != SB200_UPDATE_DP_POST) {
+    // ---- weighting_grad (gaussian_utils.py:56-62) ----
+    if (mode != SB200_UPDATE_DP_POST) {
         const float gw = cur0 / (glob0 + 1e-6f + cur0);
 #pragma unroll
         for (int c = 0; c < 13; c++) g[c] *= gw;
     }
 
-    if (a.mode == SB200_UPDATE_DP_PRE) {
+    if (mode == SB200_UPDATE_DP_PRE) {
 #pragma unroll
-        for (int grp = 0, c = 0; grp < 5; grp++) {
-            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
-            float* blk = a.fused + (size_t)c_grp_off[grp] * Pz;
-            for (int k = 0; k < nc; k++, c++) blk[(size_t)i * nc + k] = g[c];
+        for (int c = 0; c < 13; c++) {
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            a.fused[(size_t)SB_GRP_C0(grp) * Pz + iz * nc + (c - SB_GRP_C0(grp))] = g[c];
         }
-        a.fused[13 * Pz + 2 * (size_t)i] = cur0;
-        a.fused[13 * Pz + 2 * (size_t)i + 1] = cur1;
-        a.fused[15 * Pz + i] = visible ? 1.0f : 0.0f;
+        a.fused[13 * Pz + 2 * iz] = cur0;
+        a.fused[13 * Pz + 2 * iz + 1] = cur1;
+        a.fused[15 * Pz + iz] = visible ? 1.0f : 0.0f;
         return;
     }
 
-    // ---- masked Adam (adam.cu:9-38) ----
-    // All 39 loads are issued before the first store: the pointers may alias as far as the compiler knows, so a
-    // load-update-store loop per scalar serialises 13 memory round trips (first version: 0.20 ms, 1.1 TB/s).
-    if (visible && !a.stable[i]) {
-        float pv[13], mv[13], vv[13];
+    // ---- masked Adam without bias correction (adam.cu:9-38) ----
+    if (adam) {
 #pragma unroll
         for (int c = 0; c < 13; c++) {
-            const int grp = c < 3 ? 0 : c < 6 ? 1 : c < 7 ? 2 : c < 9 ? 3 : 4;
-            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
-            const int k = c - (grp == 0 ? 0 : grp == 1 ? 3 : grp == 2 ? 6 : grp == 3 ? 7 : 9);
-            const size_t e = (size_t)i * nc + k;
-            pv[c] = a.param[grp][e];
-            mv[c] = a.m[grp][e];
-            vv[c] = a.v[grp][e];
-        }
-#pragma unroll
-        for (int c = 0; c < 13; c++) {
-            const int grp = c < 3 ? 0 : c < 6 ? 1 : c < 7 ? 2 : c < 9 ? 3 : 4;
-            mv[c] = a.b1 * mv[c] + (1.0f - a.b1) * g[c];
-            vv[c] = a.b2 * vv[c] + (1.0f - a.b2) * g[c] * g[c];
-            pv[c] += -a.lr[grp] * mv[c] / (sqrtf(vv[c]) + a.eps);
-        }
-#pragma unroll
-        for (int c = 0; c < 13; c++) {
-            const int grp = c < 3 ? 0 : c < 6 ? 1 : c < 7 ? 2 : c < 9 ? 3 : 4;
-            const int nc = grp == 0 ? 3 : grp == 1 ? 3 : grp == 2 ? 1 : grp == 3 ? 2 : 4;
-            const int k = c - (grp == 0 ? 0 : grp == 1 ? 3 : grp == 2 ? 6 : grp == 3 ? 7 : 9);
-            const size_t e = (size_t)i * nc + k;
-            a.param[grp][e] = pv[c];
-            a.m[grp][e] = mv[c];
-            a.v[grp][e] = vv[c];
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+            const float m1 = a.b1 * mv[c] + (1.0f - a.b1) * g[c];
+            const float v1 = a.b2 * vv[c] + (1.0f - a.b2) * g[c] * g[c];
+            a.param[grp][e] = pv[c] + -a.lr[grp] * m1 / (sqrtf(v1) + a.eps);
+            a.m[grp][e] = m1;
+            a.v[grp][e] = v1;
         }
     }
 }
 
 int sb_launch_surfel_update(const SbUpdateArgs& a, cudaStream_t s) {
     if (a.P == 0) return 0;
-    (void)GRP_COLS;
     sb_surfel_update_kernel<<<(a.P + 255) / 256, 256, 0, s>>>(a);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
