@@ -134,6 +134,7 @@ def stage_bytes(stage, c):
         "map_loss": 100 * HW,
         "activate": 56 * P,
         "update": 49 * P + 364 * V,
+        "churn": 0,
     }[stage]
 
 

@@ -56,7 +56,8 @@ enum {
     SB200_STAGE_MAP_LOSS = 8,       /* fused mapping loss (5 kernels) */
     SB200_STAGE_ACTIVATE = 9,       /* raw parameters -> rasterizer inputs */
     SB200_STAGE_UPDATE = 10,        /* fused per-surfel update (activation backward, records, weighting, Adam) */
-    SB200_NUM_STAGES = 11
+    SB200_STAGE_CHURN = 11,         /* surfel add / prune: kNN distances, stable compaction */
+    SB200_NUM_STAGES = 12
 };
 int sb200_profile_enable(int on);
 int sb200_profile_read(double ms[SB200_NUM_STAGES], long long count[SB200_NUM_STAGES]);
@@ -168,6 +169,25 @@ int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp
                         const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
                         int64_t* kf_id, int64_t kf, float* fused, const float* lr, float b1, float b2, float eps,
                         void* stream);
+
+/* ---- surfel add / prune churn --------------------------------------------
+ * sb200_knn_mean_dist2: out[i] = mean of the squared distances from points[i] to its 3 nearest OTHER points, i.e.
+ * (KDTree(points).query(points, k=4)[0][:, 1:] ** 2).mean(1) of the reference's distCUDA2
+ * (scripts/gaussian/gaussian_utils.py:12-16), computed on the device without the host round trip.  points [N,3].
+ * Fewer than 4 points give +inf, like the KD-tree's missing neighbours. */
+int sb200_knn_mean_dist2(int N, const float* points, float* out, void* stream);
+
+/* sb200_prune_rows: stable compaction of up to SB200_PRUNE_MAX_ARRAYS per-surfel arrays by one mask, i.e.
+ * x = x[~delete_mask] for the five parameters, their ten Adam moments and the score bookkeeping at once
+ * (prune_tensors_from_optimizer + update_records("prune"), scripts/gaussian/gaussian_base.py:96-112).
+ *   delete_mask: bool [P], 1 = drop the row;  src / dst / row_bytes: HOST arrays of n_arrays device pointers / row
+ *   sizes in bytes; dst[a] must not alias src[a] (capacity buffers are used in pairs);
+ *   scratch: sb200_prune_scratch_bytes(P) bytes;  *kept_host receives the surviving row count (the only host
+ *   synchronisation; the reference synchronises once per indexed tensor). */
+#define SB200_PRUNE_MAX_ARRAYS 32
+size_t sb200_prune_scratch_bytes(int64_t P);
+int sb200_prune_rows(int P, const uint8_t* delete_mask, int n_arrays, const void* const* src, void* const* dst,
+                     const int* row_bytes, void* scratch, int* kept_host, void* stream);
 
 /* ---- building blocks exposed for parity tests ----------------------------------------------- */
 /* Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0,end_bit).  keys_in/vals_in are

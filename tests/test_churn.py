@@ -1,0 +1,134 @@
+"""Row N3 of SURVEY.md section 8f: surfel add / prune churn (GPU kNN distances, fused stable compaction, the
+capacity-doubling surfel store) against the reference's distCUDA2 (golden vector made by its own scipy KD-tree code,
+tests/golden/make_knn_golden.py) and against torch boolean indexing / cat (what the reference's
+prune_tensors_from_optimizer / cat do)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import mapper_step
+import synthetic
+import util
+
+
+def test_reference_restatement_of_distcuda2_matches_golden():
+    z = np.load(os.path.join(util.GOLDEN, "knn_dist2.npz"))
+    out = mapper_step.dist_cuda2_reference(torch.from_numpy(z["points"]))
+    assert torch.equal(out, torch.from_numpy(z["dist2"]))
+
+
+@pytest.mark.gpu
+def test_knn_matches_reference_golden():
+    mine = util.load_mine()
+    z = np.load(os.path.join(util.GOLDEN, "knn_dist2.npz"))
+    out = mine.store.knn_mean_dist2(torch.from_numpy(z["points"]).cuda()).cpu()
+    ref = torch.from_numpy(z["dist2"])
+    # the KD-tree works in float64 on the float32 coordinates; the kernel in float32: a few ulp
+    assert torch.allclose(out, ref, rtol=2e-6, atol=1e-12), float(((out - ref).abs() / ref).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 257, 40000])
+def test_knn_sizes(n):
+    mine = util.load_mine()
+    g = torch.Generator(device="cpu").manual_seed(n)
+    pts = torch.rand(n, 3, generator=g) * 10
+    out = mine.store.knn_mean_dist2(pts.cuda()).cpu()
+    assert out.shape == (n,)
+    if n == 0:
+        return
+    if n < 4:
+        assert torch.isinf(out).all()  # KDTree.query pads missing neighbours with inf
+        return
+    if n <= 5000:
+        ref = mapper_step.dist_cuda2_reference(pts)
+    else:  # float64 brute force on the GPU for the mapper's real size (40 000 new points per keyframe)
+        p = pts.cuda().double()
+        ref = torch.empty(n, dtype=torch.float64, device="cuda")
+        for s in range(0, n, 4000):
+            d = torch.cdist(p[s:s + 4000], p).pow(2)
+            ref[s:s + 4000] = d.topk(4, dim=1, largest=False).values[:, 1:].mean(1)
+        ref = ref.float().cpu()
+    assert torch.allclose(out, ref, rtol=5e-6, atol=1e-12)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,frac", [(1, 0.0), (1, 1.0), (1023, 0.5), (1024, 0.01), (1025, 0.99), (300000, 0.3)])
+def test_store_prune_and_append_equal_torch_indexing(P, frac):
+    mine = util.load_mine()
+    dev = torch.device("cuda")
+    spec = dict(a=(3, torch.float32), b=(1, torch.float32), c=(4, torch.float32), flag=(1, torch.bool),
+                idx=(1, torch.int64), s=(2, torch.float32))
+    g = torch.Generator(device="cpu").manual_seed(P)
+    rows = dict(a=torch.randn(P, 3, generator=g), b=torch.randn(P, 1, generator=g), c=torch.randn(P, 4, generator=g),
+                flag=torch.rand(P, 1, generator=g) < 0.5, idx=torch.randint(0, 1 << 40, (P, 1), generator=g),
+                s=torch.randn(P, 2, generator=g))
+    rows = {k: v.to(dev) for k, v in rows.items()}
+    st = mine.store.SurfelStore(spec, dev, capacity=64)
+    st.append(rows)  # grows 64 -> >= P
+    assert st.P == P and st.capacity >= P
+    for k in spec:
+        assert torch.equal(st.view(k), rows[k])
+    mask = (torch.rand(P, generator=g) < frac).to(dev)
+    newP = st.prune(mask)
+    assert newP == int((~mask).sum())
+    for k in spec:
+        assert torch.equal(st.view(k), rows[k][~mask]), k
+    # rows appended behind the survivors; arrays not given are zero-filled
+    extra = dict(a=torch.ones(7, 3, device=dev), c=torch.full((7, 4), 2.0, device=dev))
+    st.append(extra)
+    assert st.P == newP + 7
+    assert torch.equal(st.view("a")[newP:], extra["a"]) and torch.equal(st.view("c")[newP:], extra["c"])
+    assert float(st.view("b")[newP:].abs().sum()) == 0 and not st.view("flag")[newP:].any()
+    for k in spec:
+        assert torch.equal(st.view(k)[:newP], rows[k][~mask]), k
+    # and once more from the other buffer set
+    mask2 = (torch.rand(st.P, generator=g) < 0.5).to(dev)
+    before = {k: st.view(k).clone() for k in spec}
+    st.prune(mask2)
+    for k in spec:
+        assert torch.equal(st.view(k), before[k][~mask2]), k
+
+
+@pytest.mark.gpu
+def test_mapper_churn_cycle_fused_matches_torch_path():
+    """train -> prune -> densify -> train on both paths: same surfel counts, same new-surfel parameters, same
+    bookkeeping, Adam moments carried through the prune and reset by the densify (setup_optimizer)."""
+    mine = util.load_mine()
+    scene, views = synthetic.make_scene("C3", P=20000, W=160, H=96)
+    dev = torch.device("cuda")
+    a = mapper_step.SurfelMapper(mine, scene, dev, supervision="rgb+depth", fused=False)
+    b = mapper_step.SurfelMapper(mine, scene, dev, supervision="rgb+depth", fused=True)
+    g = torch.Generator(device="cpu").manual_seed(9)
+
+    def train(i):
+        v = views[-1 - i]
+        gt = {k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()}
+        vd = mapper_step.view_to_device(v, dev)
+        return float(a.train_view(vd, gt, kf_id=i + 1)), float(b.train_view(vd, gt, kf_id=i + 1))
+
+    train(0)
+    mask = (torch.rand(a.P, generator=g) < 0.2).to(dev)
+    kept_m = a.optimizer.state[a._xyz]["exp_avg"][~mask].clone()
+    assert a.prune(mask) == b.prune(mask) == int((~mask).sum())
+    assert util.rel_err(b.optimizer.state[b._xyz]["exp_avg"], kept_m) < 2e-3  # moments survive a prune
+    assert util.rel_err(b._global_scores, a._global_scores) < 1e-4
+    la, lb = train(1)
+    assert abs(la - lb) <= 2e-5 * max(1.0, abs(la))
+    n_new = 3000
+    xyz = (scene["means3D"][:n_new] + 0.01 * torch.randn(n_new, 3, generator=g)).to(dev)
+    rgb, rots = torch.rand(n_new, 3, generator=g).to(dev), torch.randn(n_new, 4, generator=g).to(dev)
+    P0 = a.P
+    assert a.add_surfels(xyz, rgb, rots) == b.add_surfels(xyz, rgb, rots) == P0 + n_new
+    for k in mapper_step.GROUPS:
+        pa, pb = getattr(a, k).data, getattr(b, k).data
+        assert pa.shape == pb.shape
+        assert torch.allclose(pb[P0:], pa[P0:], rtol=2e-6, atol=1e-7), k   # incl. log-scales from the kNN distances
+        assert util.rel_err(pb[:P0], pa[:P0]) < 1e-5, k
+        assert float(b.optimizer.state[getattr(b, k)]["exp_avg"].abs().sum()) == 0.0, k  # fresh optimizer
+    assert float(b._local_scores[P0:].abs().sum()) == 0.0 and not b._stable_mask[P0:].any()
+    la, lb = train(2)
+    assert abs(la - lb) <= 2e-5 * max(1.0, abs(la))
+    assert b._ws.P == b.P == a.P

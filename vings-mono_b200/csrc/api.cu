@@ -55,7 +55,7 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 3; }
+int sb200_abi_version(void) { return 4; }
 
 long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 

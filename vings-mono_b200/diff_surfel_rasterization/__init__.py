@@ -82,7 +82,13 @@ def _load():
     lib.sb200_surfel_update.restype = _i32
     lib.sb200_surfel_update.argtypes = ([_i32, _i32] + [_vp] * 3 + [_vp] * 5 + [_vp] * 7 + [_i64, _vp, _vp] +
                                         [_f32] * 3 + [_vp])
-    if lib.sb200_abi_version() != 3:
+    lib.sb200_knn_mean_dist2.restype = _i32
+    lib.sb200_knn_mean_dist2.argtypes = [_i32, _vp, _vp, _vp]
+    lib.sb200_prune_scratch_bytes.restype = _sz
+    lib.sb200_prune_scratch_bytes.argtypes = [_i64]
+    lib.sb200_prune_rows.restype = _i32
+    lib.sb200_prune_rows.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp]
+    if lib.sb200_abi_version() != 4:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -124,7 +130,7 @@ def _count_buffer(device):
 
 
 STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam",
-          "map_loss", "activate", "update")
+          "map_loss", "activate", "update", "churn")
 
 
 def profile_enable(on=True):
@@ -354,6 +360,7 @@ class SparseGaussianAdam(torch.optim.Adam):
 
 
 from . import mapping  # noqa: E402  (fused mapping-step blocks: N1/N2 of SURVEY.md section 8f)
+from . import store  # noqa: E402  (surfel add / prune churn: N3)
 
 __all__ = ["GaussianRasterizationSettings", "GaussianRasterizer", "SparseGaussianAdam", "rasterize_gaussians",
-           "mapping"]
+           "mapping", "store"]

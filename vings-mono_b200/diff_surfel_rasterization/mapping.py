@@ -66,24 +66,45 @@ class RasterWorkspace:
     per-call allocation.  Only the sort scratch and the sorted id list depend on the data (R); they grow
     geometrically and are kept."""
 
-    def __init__(self, P, W, H, device):
+    def __init__(self, P, W, H, device, capacity=None):
         lib = _load()
-        self.P, self.W, self.H, self.device = P, W, H, device
+        self.W, self.H, self.device = W, H, device
         u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=device)
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=device)
-        self.geom = u8(lib.sb200_geom_bytes(P))
         self.image = u8(lib.sb200_image_bytes(W, H))
-        self.grad_ws = u8(lib.sb200_grad_bytes(P))
         self.loss_ws = u8(lib.sb200_map_loss_bytes(W, H))
         self.binning = u8(0)
         self.point_list = torch.empty(0, dtype=torch.int32, device=device)
         self.color, self.allmap = f(3, H, W), f(7, H, W)
-        self.radii = torch.empty(P, dtype=torch.int32, device=device)
-        self.d_means3D, self.d_means2D, self.d_colors, self.d_opacity = f(P, 3), f(P, 3), f(P, 3), f(P, 1)
-        self.d_scales, self.d_rot, self.scores = f(P, 2), f(P, 4), f(P, 2)
         self.loss_out = (f(7), f(3, H, W), f(7, H, W))
         self.pixel_mask = torch.ones(H * W, dtype=torch.bool, device=device)
         self.R = 0
+        self.capacity = 0
+        self._alloc_rows(max(int(capacity or 0), P, 1))
+        self.set_P(P)
+
+    def _alloc_rows(self, cap):
+        """P-sized buffers for up to ``cap`` surfels (the layouts are monotone in P, so any P <= cap fits)."""
+        lib = _load()
+        dev = self.device
+        f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
+        self.capacity = cap
+        self.geom = torch.empty(lib.sb200_geom_bytes(cap), dtype=torch.uint8, device=dev)
+        self.grad_ws = torch.empty(lib.sb200_grad_bytes(cap), dtype=torch.uint8, device=dev)
+        self._rows = dict(radii=torch.empty(cap, dtype=torch.int32, device=dev), d_means3D=f(cap, 3), d_means2D=f(cap, 3),
+                          d_colors=f(cap, 3), d_opacity=f(cap, 1), d_scales=f(cap, 2), d_rot=f(cap, 4), scores=f(cap, 2),
+                          act_opacity=f(cap, 1), act_scales=f(cap, 2), act_rot=f(cap, 4))
+
+    def set_P(self, P):
+        """Surfel count of the next forward (changes with every prune / densify); grows geometrically, never shrinks."""
+        if P > self.capacity:
+            cap = self.capacity
+            while cap < P:
+                cap *= 2
+            self._alloc_rows(cap)
+        self.P = P
+        for name, buf in self._rows.items():
+            setattr(self, name, buf[:P])
 
     def forward(self, means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix):
         lib = _load()

@@ -70,6 +70,14 @@ def get_loss(weights, pred, gt, window):
             weights["depth_loss"] * depth_loss + weights["dist_loss"] * dist_loss)
 
 
+def dist_cuda2_reference(points):
+    """distCUDA2 of the reference, verbatim semantics (gaussian_utils.py:12-16): scipy KD-tree on the host."""
+    from scipy.spatial import KDTree
+    points_np = points.detach().cpu().float().numpy()
+    dists, _ = KDTree(points_np).query(points_np, k=4)
+    return torch.tensor((dists[:, 1:] ** 2).mean(1), dtype=points.dtype, device=points.device)
+
+
 def depth_propagate_normal(depth, fx, fy, cx, cy):
     """normal_utils.py:6-21 + tf.py:133-146 (depth -> camera points -> central-difference cross product)"""
     H, W = depth.shape
@@ -105,36 +113,66 @@ class SurfelMapper:
         self.set_surfels(scene)
 
     # ---- surfel storage (raw, pre-activation parameters as gaussian_base.py:44-48,55-62) ----
+    BOOK = dict(_local_scores=(2, torch.float32), _global_scores=(2, torch.float32), _stable_mask=(1, torch.bool),
+                _globalkf_id=(1, torch.int64), _globalkf_max_scores=(1, torch.float32))
+
     def set_surfels(self, scene):
         dev = self.device
-        P = scene["means3D"].shape[0]
         raw = dict(_xyz=scene["means3D"], _rgb=scene["colors"],
                    _opacity=torch.logit(scene["opacities"].clamp(1e-6, 1 - 1e-6)),
                    _scaling=torch.log(scene["scales"]), _rotation=scene["rotations"])
-        self.P = P
+        raw = {k: v.to(dev).float().contiguous() for k, v in raw.items()}
+        P = raw["_xyz"].shape[0]
+        if self.fused:
+            # every per-surfel array lives in one capacity-doubling store (diff_surfel_rasterization/store.py)
+            spec = {k: (GROUP_COLS[k], torch.float32) for k in GROUPS}
+            spec.update({"m" + k: (GROUP_COLS[k], torch.float32) for k in GROUPS})
+            spec.update({"v" + k: (GROUP_COLS[k], torch.float32) for k in GROUPS})
+            spec.update(self.BOOK)
+            self.store = self.mod.store.SurfelStore(spec, dev, capacity=max(1 << 16, int(P * 1.25)))
+            self.store.append(raw)
+            self._ws = self.mod.mapping.RasterWorkspace(P, self.W, self.H, dev, capacity=self.store.capacity)
+            self._bind_store()
+        else:
+            self._bind_tensors({k: raw[k].clone() for k in GROUPS}, None,
+                               dict(_local_scores=torch.zeros(P, 2, device=dev), _global_scores=torch.zeros(P, 2, device=dev),
+                                    _stable_mask=torch.zeros(P, dtype=torch.bool, device=dev),
+                                    _globalkf_id=torch.zeros(P, dtype=torch.long, device=dev),
+                                    _globalkf_max_scores=torch.zeros(P, device=dev)))
+
+    def _bind_tensors(self, params, moments, book):
+        """(Re)create parameters, optimizer and bookkeeping from tensors -- what setup_optimizer /
+        prune_tensors_from_optimizer leave behind (gaussian_base.py:52-62,96-112).  moments: {name: (m, v)} or None
+        for a fresh optimizer."""
+        self.P = params["_xyz"].shape[0]
         for k in GROUPS:
-            setattr(self, k, torch.nn.Parameter(raw[k].to(dev).float().contiguous().clone().requires_grad_(True)))
+            setattr(self, k, torch.nn.Parameter(params[k].requires_grad_(True)))
         self.optimizer = self.mod.SparseGaussianAdam(
             [{"params": [getattr(self, k)], "lr": LR[k], "name": k} for k in GROUPS], lr=0.0, eps=1e-15)
-        self._local_scores = torch.zeros(P, 2, device=dev)
-        self._global_scores = torch.zeros(P, 2, device=dev)
-        self._stable_mask = torch.zeros(P, dtype=torch.bool, device=dev)
-        self._globalkf_id = torch.zeros(P, dtype=torch.long, device=dev)
-        self._globalkf_max_scores = torch.zeros(P, device=dev)
-        if self.fused:
-            mp = self.mod.mapping
-            self._ws = mp.RasterWorkspace(P, self.W, self.H, dev)
-            self._act = (torch.empty(P, 1, device=dev), torch.empty(P, 2, device=dev), torch.empty(P, 4, device=dev))
-            for group in self.optimizer.param_groups:  # the state SparseGaussianAdam.step creates lazily
-                prm = group["params"][0]
-                st = self.optimizer.state[prm]
-                if len(st) == 0:
-                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
-                    st["exp_avg"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
-                    st["exp_avg_sq"] = torch.zeros_like(prm, memory_format=torch.preserve_format)
+        if moments is not None:
+            for k in GROUPS:
+                self.optimizer.state[getattr(self, k)] = dict(step=torch.tensor(0.0), exp_avg=moments[k][0],
+                                                              exp_avg_sq=moments[k][1])
+        for name, t in book.items():
+            setattr(self, name, t)
+        self._bind_dp()
+
+    def _bind_store(self):
+        st = self.store
+        P = st.P
+        self._ws.set_P(P)
+        self._act = (self._ws.act_opacity, self._ws.act_scales, self._ws.act_rot)
+        self._bind_tensors({k: st.view(k) for k in GROUPS}, {k: (st.view("m" + k), st.view("v" + k)) for k in GROUPS},
+                           dict(_local_scores=st.view("_local_scores"), _global_scores=st.view("_global_scores"),
+                                _stable_mask=st.view("_stable_mask").reshape(P),
+                                _globalkf_id=st.view("_globalkf_id").reshape(P),
+                                _globalkf_max_scores=st.view("_globalkf_max_scores").reshape(P)))
+
+    def _bind_dp(self):
         if self.world_size > 1:
             # fused gradient buffer: parameter .grad tensors are column blocks of one allocation so that a
             # single NCCL all-reduce moves gradients, scores and visibility (SURVEY.md section 8e)
+            P, dev = self.P, self.device
             self._fused = torch.zeros(16 * P, device=dev)
             self._grad_views, off = {}, 0
             for k in GROUPS:
@@ -143,6 +181,50 @@ class SurfelMapper:
                 off += n
             self._score_view = self._fused[off:off + 2 * P].view(P, 2)
             self._vis_view = self._fused[off + 2 * P:off + 3 * P]
+
+    # ---- churn: gaussian_model.py:92-161 (add_new_frame), gaussian_base.py:74-112 ----
+    @torch.no_grad()
+    def prune(self, delete_mask):
+        """x = x[~delete_mask] for parameters, Adam moments and score bookkeeping
+        (prune_tensors_from_optimizer + update_records("prune")).  Returns the new P."""
+        if self.fused:
+            self.store.prune(delete_mask)
+            self._bind_store()
+            return self.P
+        keep = ~delete_mask
+        moments = None
+        if all(len(self.optimizer.state[getattr(self, k)]) for k in GROUPS):
+            moments = {k: (self.optimizer.state[getattr(self, k)]["exp_avg"][keep],
+                           self.optimizer.state[getattr(self, k)]["exp_avg_sq"][keep]) for k in GROUPS}
+        self._bind_tensors({k: getattr(self, k).data[keep] for k in GROUPS}, moments,
+                           {n: getattr(self, n)[keep] for n in self.BOOK})
+        return self.P
+
+    @torch.no_grad()
+    def add_surfels(self, xyz, rgb, unnorm_rots):
+        """The tail of add_new_frame (gaussian_model.py:136-161): isotropic log-scale from the mean squared distance
+        to the 3 nearest new points, opacity 0.8, concatenation, zero bookkeeping rows, and a FRESH optimizer for
+        every surfel (the reference ends with setup_optimizer(), which drops all Adam moments).  Returns the new P."""
+        n = xyz.shape[0]
+        if self.fused:
+            dist2 = torch.clamp_min(self.mod.store.knn_mean_dist2(xyz), 0.0000001)
+        else:
+            dist2 = torch.clamp_min(dist_cuda2_reference(xyz), 0.0000001)
+        new = dict(_xyz=xyz, _rgb=rgb, _scaling=torch.log(1.0 * torch.sqrt(dist2))[..., None].repeat(1, 2),
+                   _rotation=unnorm_rots,
+                   _opacity=torch.log(torch.full((n, 1), 0.8, device=xyz.device) / (1 - 0.8)).to(torch.float))
+        if self.fused:
+            self.store.append(new)
+            for k in GROUPS:
+                self.store.view("m" + k).zero_()
+                self.store.view("v" + k).zero_()
+            self._bind_store()
+            return self.P
+        book = {name: torch.cat((getattr(self, name), torch.zeros((n,) + tuple(getattr(self, name).shape[1:]),
+                                                                    dtype=getattr(self, name).dtype, device=self.device)))
+                for name in self.BOOK}
+        self._bind_tensors({k: torch.cat((getattr(self, k).data, new[k]), dim=0) for k in GROUPS}, None, book)
+        return self.P
 
     def params(self):
         return [getattr(self, k) for k in GROUPS]
