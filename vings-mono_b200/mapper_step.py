@@ -117,12 +117,24 @@ class SurfelMapper:
                 _globalkf_id=(1, torch.int64), _globalkf_max_scores=(1, torch.float32))
 
     def set_surfels(self, scene):
+        """scene: ACTIVATED surfels (synthetic.make_scene): means3D, colors, opacities, scales, rotations."""
+        self.set_raw(dict(_xyz=scene["means3D"], _rgb=scene["colors"],
+                          _opacity=torch.logit(scene["opacities"].clamp(1e-6, 1 - 1e-6)),
+                          _scaling=torch.log(scene["scales"]), _rotation=scene["rotations"]))
+
+    def set_raw(self, raw, book=None):
+        """raw: the five RAW parameter tensors (what checkpoints and PLY files hold, formats.py); book: optional score
+        bookkeeping tensors (load_pt_ckpt).  A fresh optimizer either way, like load_*_ckpt's setup_optimizer()."""
         dev = self.device
-        raw = dict(_xyz=scene["means3D"], _rgb=scene["colors"],
-                   _opacity=torch.logit(scene["opacities"].clamp(1e-6, 1 - 1e-6)),
-                   _scaling=torch.log(scene["scales"]), _rotation=scene["rotations"])
-        raw = {k: v.to(dev).float().contiguous() for k, v in raw.items()}
+        raw = {k: raw[k].detach().to(dev).float().contiguous() for k in GROUPS}
         P = raw["_xyz"].shape[0]
+        raw["_opacity"] = raw["_opacity"].reshape(P, 1)
+        zeros = dict(_local_scores=torch.zeros(P, 2, device=dev), _global_scores=torch.zeros(P, 2, device=dev),
+                     _stable_mask=torch.zeros(P, dtype=torch.bool, device=dev),
+                     _globalkf_id=torch.zeros(P, dtype=torch.long, device=dev),
+                     _globalkf_max_scores=torch.zeros(P, device=dev))
+        if book is not None:
+            zeros = {k: book[k].detach().to(dev).to(zeros[k].dtype).reshape(zeros[k].shape).contiguous() for k in zeros}
         if self.fused:
             # every per-surfel array lives in one capacity-doubling store (diff_surfel_rasterization/store.py)
             spec = {k: (GROUP_COLS[k], torch.float32) for k in GROUPS}
@@ -130,15 +142,13 @@ class SurfelMapper:
             spec.update({"v" + k: (GROUP_COLS[k], torch.float32) for k in GROUPS})
             spec.update(self.BOOK)
             self.store = self.mod.store.SurfelStore(spec, dev, capacity=max(1 << 16, int(P * 1.25)))
-            self.store.append(raw)
+            rows = dict(raw)
+            rows.update(zeros)
+            self.store.append(rows)
             self._ws = self.mod.mapping.RasterWorkspace(P, self.W, self.H, dev, capacity=self.store.capacity)
             self._bind_store()
         else:
-            self._bind_tensors({k: raw[k].clone() for k in GROUPS}, None,
-                               dict(_local_scores=torch.zeros(P, 2, device=dev), _global_scores=torch.zeros(P, 2, device=dev),
-                                    _stable_mask=torch.zeros(P, dtype=torch.bool, device=dev),
-                                    _globalkf_id=torch.zeros(P, dtype=torch.long, device=dev),
-                                    _globalkf_max_scores=torch.zeros(P, device=dev)))
+            self._bind_tensors({k: raw[k].clone() for k in GROUPS}, None, zeros)
 
     def _bind_tensors(self, params, moments, book):
         """(Re)create parameters, optimizer and bookkeeping from tensors -- what setup_optimizer /
