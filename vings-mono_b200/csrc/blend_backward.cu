@@ -23,6 +23,7 @@
 //     record (3 sectors); there is no cross-warp combine and no shared accumulation buffer;
 //   * every warp stops at ITS OWN last contributor (warp max), not the tile's.
 #include "pair_math.cuh"
+#include "ring.cuh"
 
 #define BB_CWARPS 8
 #define BB_THREADS (BB_CWARPS * 32)
@@ -30,33 +31,6 @@
 #ifndef BB_STAGES
 #define BB_STAGES 8
 #endif
-
-__device__ __forceinline__ uint32_t bb_smem(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void bb_mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bb_smem(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void bb_mbar_arrive(uint64_t* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bb_smem(bar)) : "memory");
-}
-__device__ __forceinline__ void bb_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bb_smem(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void bb_mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "BB_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra BB_DONE_%=;\n"
-        "bra BB_WAIT_%=;\n"
-        "BB_DONE_%=:\n"
-        "}\n" ::"r"(bb_smem(bar)), "r"(parity) : "memory");
-}
-// 1-D bulk copy global -> shared through the TMA engine; completion is signalled on `bar` in bytes
-__device__ __forceinline__ void bb_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(bb_smem(dst)), "l"(src), "r"(bytes), "r"(bb_smem(bar)) : "memory");
-}
 
 // Gradient-side arithmetic is not gated (only k, l, p, s, rho, G, alpha decide which pairs blend, and those stay
 // bit-pinned in pair_math.cuh), so its divisions use the MUFU reciprocal: the gradients are compared with the

@@ -18,19 +18,23 @@
 //   5. no per-32-splat checkpoints are written (the backward re-walks the tile instead), removing the
 //      reference's 13 KiB-per-bucket SampleState traffic; termination is tracked per warp and per CTA.
 #include "pair_math.cuh"
-#include <cuda_pipeline.h>
+#include "ring.cuh"
 
 #define FB_THREADS 256
-#define FB_BATCH 128
-#define FB_Q 7  // quads 0..6 of the record go to s_q, quad 7 (box) to s_bb
+#define FB_WARPS 8
+#define FB_BATCH 32
+#define FB_STAGES 8
 
 __global__ void __launch_bounds__(FB_THREADS)
 sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                         const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                         float* __restrict__ out_color, float* __restrict__ out_others) {
-    __shared__ __align__(16) float4 s_q[2][FB_BATCH][FB_Q];
-    __shared__ __align__(16) float4 s_bb[2][FB_BATCH];
+    __shared__ __align__(128) float4 s_rec[FB_STAGES][FB_BATCH][SB_REC_F4];
+    __shared__ __align__(8) uint64_t s_full[FB_STAGES];
+    __shared__ uint32_t s_cnt[FB_STAGES];
+    __shared__ uint32_t s_donemask;  // warps whose 32 pixels have all terminated
+    __shared__ int s_limit;          // first batch that is NOT loaded (set once every warp is done)
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 #ifdef SB_DEBUG_NO_LPT
@@ -52,17 +56,27 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     const int n = (int)(range.y - range.x);
     const int nbatches = (n + FB_BATCH - 1) / FB_BATCH;
 
-    auto issue = [&](int b) {
+    if (tid < FB_STAGES) {
+        bb_mbar_init(&s_full[tid], 1);
+        s_cnt[tid] = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid == 0) {
+        s_donemask = 0;
+        s_limit = nbatches;
+    }
+    __syncthreads();
+    // gather the records of batch b into ring stage b % FB_STAGES (called by one whole warp)
+    auto fill = [&](int b) {
+        const int st = b % FB_STAGES;
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
-        const uint32_t* ids = point_list + range.x + b * FB_BATCH;
-        for (int e = tid; e < cnt * SB_REC_F4; e += FB_THREADS) {
-            int sp = e >> 3, q = e & 7;
-            uint32_t id = __ldg(ids + sp);
-            float4* dst = (q < FB_Q) ? &s_q[b & 1][sp][q] : &s_bb[b & 1][sp];
-            __pipeline_memcpy_async(dst, rec + (size_t)id * SB_REC_F4 + q, 16);
-        }
-        __pipeline_commit();
+        uint32_t id = 0;
+        if (lane < cnt) id = __ldg(point_list + range.x + b * FB_BATCH + lane);
+        if (lane == 0) bb_mbar_expect_tx(&s_full[st], (uint32_t)cnt * (SB_REC_F4 * 16));
+        __syncwarp();
+        if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
     };
+    for (int b0 = wid; b0 < FB_STAGES && b0 < nbatches; b0 += FB_WARPS) fill(b0);  // prime the ring
 
     float T = 1.0f;
     uint32_t last_contributor = 0;
@@ -71,25 +85,26 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     float D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
     float median_contributor = -1.f;
 
-    if (nbatches > 0) issue(0);
+    bool wdone = __all_sync(0xffffffffu, done);
+    if (wdone && lane == 0) atomicOr(&s_donemask, 1u << wid);
     for (int b = 0; b < nbatches; b++) {
-        if (b + 1 < nbatches) {
-            issue(b + 1);
-            __pipeline_wait_prior(1);
-        } else {
-            __pipeline_wait_prior(0);
+        const int st = b % FB_STAGES;
+        // wait for the batch -- or learn that every pixel of the tile has terminated (forward.cu:348-350: the
+        // reference votes with a CTA barrier per 256 surfels; here the last warp to finish a batch stops the
+        // refills once all eight warps are done, and nobody waits for a batch that will not come)
+        bool stop = false;
+        while (!bb_mbar_try(&s_full[st], (uint32_t)(b / FB_STAGES) & 1u)) {
+            if (b >= *(volatile int*)&s_limit) { stop = true; break; }
         }
-        // barrier doubles as the CTA-wide termination vote (forward.cu:348-350)
-        if (__syncthreads_count(done) == FB_THREADS) break;
+        if (stop) break;
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
-        const float4(*sq)[FB_Q] = s_q[b & 1];
-        const float4* sbb = s_bb[b & 1];
-        for (int c = 0; c < cnt; c += 32) {
-            if (__all_sync(0xffffffffu, done)) break;
+        const float4(*sq)[SB_REC_F4] = s_rec[st];
+        if (!wdone) {
+            const int c = 0;
             // ---- warp-level cull: lane tests surfel c+lane's box against the warp's pixel block ----
             bool ov = false;
             if (c + lane < cnt) {
-                const float4 bb = sbb[c + lane];
+                const float4 bb = sq[c + lane][SB_REC_BBOX];
                 ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
 #ifdef SB_BLOCK_CULL  // opt-in: measured neutral
                 if (ov) ov = !sb_block_culled(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bx0, bx1, by0, by1);
@@ -185,10 +200,29 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
                 T = test_T;
                 last_contributor = contributor;
             }
+            wdone = __all_sync(0xffffffffu, done);
+            if (wdone && lane == 0) atomicOr(&s_donemask, 1u << wid);
         }
-        __syncthreads();  // everyone finished reading buffer b&1 before batch b+2 lands in it
+        // hand the stage back: the last of the 8 warps to get here refills it with the batch FB_STAGES ahead
+        __syncwarp();
+        uint32_t old = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            old = atomicAdd(&s_cnt[st], 1u);
+        }
+        old = __shfl_sync(0xffffffffu, old, 0);
+        if (old == FB_WARPS - 1) {
+            if (lane == 0) s_cnt[st] = 0;
+            __threadfence_block();
+            if (b + FB_STAGES < nbatches) {
+                if (*(volatile uint32_t*)&s_donemask == (1u << FB_WARPS) - 1u) {
+                    if (lane == 0) atomicMin(&s_limit, b + FB_STAGES);
+                } else {
+                    fill(b + FB_STAGES);
+                }
+            }
+        }
     }
-    __pipeline_wait_prior(0);
 
     if (inside) {
         const size_t HW = (size_t)H * W;
