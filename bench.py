@@ -62,7 +62,7 @@ class ClockSampler:
         self.rows, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "25"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.th = threading.Thread(target=self._read, daemon=True)
             self.th.start()
@@ -376,14 +376,24 @@ def main():
                 stages[name] = {"ms_per_launch": per, "launches": cnt,
                                 "GBps": stage_bytes(name, counters) / (per * 1e-3) / 1e9}
         dom = max((n for n in stages if n != "adam"), key=lambda n: stages[n]["ms_per_launch"])
-        traffic = None
+        traffic, winst = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpath):
-            traffic = json.load(open(tpath)).get(args.config, {}).get(dom)
+            tj = json.load(open(tpath))
+            traffic = tj.get(args.config, {}).get(dom)
+            winst = tj.get(args.config + "_warp_inst", {}).get(dom)
         out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": stages[dom]["GBps"], "peak": peak,
                            "unit": "GB/s", "frac": stages[dom]["GBps"] / peak, "traffic": traffic,
                            "peak_source": peak_src,
                            "algorithmic_bytes_per_launch": stage_bytes(dom, counters)}
+        if winst:
+            # the blend kernels are bound by instruction issue, not HBM: executed warp
+            # instructions per launch (ncu capture, profiles/traffic.json) / live launch time vs 148 SMs x 4 schedulers
+            sm_mhz = (clk or {}).get("sm_mhz") or 1965.0
+            peak_issue = 148 * 4 * sm_mhz * 1e6
+            out["roofline"]["issue"] = {"warp_inst_per_launch": winst, "achieved_ginst_s": winst / (stages[dom]["ms_per_launch"] * 1e-3) / 1e9,
+                                        "peak_ginst_s": peak_issue / 1e9,
+                                        "frac": winst / (stages[dom]["ms_per_launch"] * 1e-3) / peak_issue}
         out["stages"] = stages
         a_iter = iteration_bytes(counters)
         out["raster"]["algorithmic_bytes_per_iter"] = a_iter
