@@ -121,10 +121,15 @@ def stage_bytes(stage, c):
     """Algorithmic bytes per launch (SURVEY.md section 8d / DESIGN.md section 5)."""
     P, V, R, HW, tiles, n_p = c["P"], c["V"], c["R"], c["HW"], c["tiles"], c["sort_passes"]
     return {
-        "preprocess": 48 * P + 64 * V + 8 * P,
-        "duplicate": 8 * P + 12 * V + 12 * R,
-        "sort": (24 * n_p + 8) * R,
-        "ranges": 8 * R + 8 * tiles,
+        # inputs 52 + radii, tile count, sort key out per surfel; record 128 + depth 4 + rect 8 per visible surfel
+        "preprocess": 64 * P + 140 * V,
+        # histogram 4P; pass 0 reads P keys, writes V (key, id); passes 1-2 move 16 B; the last reads 8, writes 4
+        "surfel_sort": 8 * P + 52 * V,
+        # sorted id, tile count, rect per visible surfel; (tile, id) out and one tile-count RED per pair
+        "duplicate": 16 * V + 12 * R,
+        # pair sort by tile id: (tile, id) in and out per pass, the last pass writes ids only
+        "sort": (16 * (n_p - 1) + 12) * R,
+        "ranges": 16 * tiles,
         "blend_fwd": 4 * R + 76 * V + 60 * HW,
         "blend_bwd": 4 * R + 76 * V + 101 * HW + 80 * V,
         "preprocess_bwd": 156 * V + 72 * P,
@@ -139,7 +144,8 @@ def stage_bytes(stage, c):
 
 
 def iteration_bytes(c):
-    return 136 * c["P"] + 464 * c["V"] + (36 + 24 * c["sort_passes"]) * c["R"] + 161 * c["HW"] + 8 * c["tiles"]
+    # the reference algorithm's compulsory traffic (64-bit key sort, ref_sort_passes passes)
+    return 136 * c["P"] + 464 * c["V"] + (36 + 24 * c["ref_sort_passes"]) * c["R"] + 161 * c["HW"] + 8 * c["tiles"]
 
 
 def higher_msb(n):
@@ -357,7 +363,7 @@ def main():
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     counters = {"P": P, "V": sum(V_seen) / len(V_seen), "HW": W * H, "tiles": tiles,
                 "R": (sum(R_timed) / len(R_timed)) if R_timed else None,
-                "sort_passes": (32 + higher_msb(tiles) + 7) // 8}
+                "sort_passes": (higher_msb(tiles) + 7) // 8, "ref_sort_passes": (32 + higher_msb(tiles) + 7) // 8}
     out["raster"] = {"metric": "rasterizer fwd+bwd iterations/s (one view, fixed upstream gradients)",
                      "value": 1e3 / raster_ms, "unit": "iters/s", "ms_per_iter": raster_ms}
     out["counters"] = counters

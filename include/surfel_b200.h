@@ -45,10 +45,10 @@ long long sb200_launch_count(void);
  * stream the stage is launched on.  sb200_profile_read waits for the recorded events, returns the summed
  * milliseconds and the number of timed launches per stage since the previous read, and resets. */
 enum {
-    SB200_STAGE_PREPROCESS = 0,     /* per-surfel preprocess + tile-count prefix sum */
-    SB200_STAGE_DUPLICATE = 1,      /* tile-key duplication */
-    SB200_STAGE_SORT = 2,           /* onesweep radix sort (histogram + passes) */
-    SB200_STAGE_RANGES = 3,         /* tile ranges */
+    SB200_STAGE_PREPROCESS = 0,     /* per-surfel preprocess (+ R) */
+    SB200_STAGE_DUPLICATE = 1,      /* (tile, surfel) pair emission in depth order + pair-offset scan + tile counts */
+    SB200_STAGE_SORT = 2,           /* stable onesweep sort of the pairs by tile id */
+    SB200_STAGE_RANGES = 3,         /* tile ranges, tile launch order, digit bases of the pair sort */
     SB200_STAGE_BLEND_FWD = 4,      /* per-tile forward blend */
     SB200_STAGE_BLEND_BWD = 5,      /* per-tile backward blend (+ zeroing of its accumulation record) */
     SB200_STAGE_PREPROCESS_BWD = 6, /* per-surfel backward preprocess */
@@ -57,7 +57,8 @@ enum {
     SB200_STAGE_ACTIVATE = 9,       /* raw parameters -> rasterizer inputs */
     SB200_STAGE_UPDATE = 10,        /* fused per-surfel update (activation backward, records, weighting, Adam) */
     SB200_STAGE_CHURN = 11,         /* surfel add / prune: kNN distances, stable compaction */
-    SB200_NUM_STAGES = 12
+    SB200_STAGE_SURFEL_SORT = 12,   /* stable onesweep sort of the visible surfels by depth (histogram + 4 passes) */
+    SB200_NUM_STAGES = 13
 };
 int sb200_profile_enable(int on);
 int sb200_profile_read(double ms[SB200_NUM_STAGES], long long count[SB200_NUM_STAGES]);
@@ -74,17 +75,19 @@ size_t sb200_binning_bytes(int64_t R);
 size_t sb200_grad_bytes(int64_t P);
 /* byte offsets of the inspectable arrays inside the workspaces (tests / debugging):
  *   geom:    [0] records float4[8P]  [1] depth f32[P]  [2] tile rect u16x4[P]  [3] tiles_touched u32[P]
- *            [4] point_offsets u32[P] (inclusive)
+ *            [4] ids of the V visible surfels in (depth, id) order u32[P] (entries past V are scratch)
  *   image:   [0] ranges uint2[tiles] [1] final T,M1,M2 f32[3HW]  [2] n_contrib,median_contrib u32[2HW]
- *   binning: [0] keys A u64[R] (unsorted keys)  [1] keys B u64[R]  [2] values A u32[R]  [3] values B u32[R] */
+ *   binning: [0] tile ids A u32[R] (pairs as emitted, depth order)  [1] tile ids B u32[R]
+ *            [2] surfel ids A u32[R] (as emitted)  [3] surfel ids B u32[R] */
 void sb200_geom_layout(int64_t P, size_t out[5]);
 void sb200_image_layout(int W, int H, size_t out[3]);
 void sb200_binning_layout(int64_t R, size_t out[4]);
 
 /* ---- forward -------------------------------------------------------------------------------- */
-/* Stage 1: per-surfel preprocess (ray-splat transform, AABB, radius, tile rect) + prefix sum of the
- * tile counts.  Writes radii[P] (int32) and the geometry workspace, then synchronises `stream` once to
- * return the number of (tile,surfel) pairs in *num_rendered_host (host pointer, pinned preferred). */
+/* Stage 1: per-surfel preprocess (ray-splat transform, AABB, radius, tile rect, R = sum of the tile counts) and
+ * the stable sort of the visible surfels by depth.  Writes radii[P] (int32) and the geometry workspace.  Waits
+ * ONCE, for the 8-byte read-back of R into *num_rendered_host (host pointer, pinned preferred), which is queued
+ * before the sort so that the GPU keeps working while the host sizes the binning scratch. */
 int sb200_forward_begin(int P, int W, int H,
                         const float* means3D,    /* [P,3] */
                         const float* scales,     /* [P,2] */
@@ -94,7 +97,7 @@ int sb200_forward_begin(int P, int W, int H,
                         const float* viewmatrix, const float* projmatrix,
                         void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream);
 
-/* Stage 2: key duplication, onesweep radix sort, tile ranges, per-tile blend.
+/* Stage 2: pair emission in depth order, tile ranges, stable sort of the pairs by tile, per-tile blend.
  * point_list[R] (u32) receives the sorted surfel ids and must persist until the backward.
  * out_color [3,H,W]; out_others [7,H,W] = depth, alpha, normal xyz (view space), median depth, distortion. */
 int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg /* [3] */,
@@ -190,10 +193,13 @@ int sb200_prune_rows(int P, const uint8_t* delete_mask, int n_arrays, const void
                      const int* row_bytes, void* scratch, int* kept_host, void* stream);
 
 /* ---- building blocks exposed for parity tests ----------------------------------------------- */
-/* Stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0,end_bit).  keys_in/vals_in are
- * clobbered; scratch = sb200_binning_bytes(n) bytes whose keys A / values A arrays (see layout) ARE
- * keys_in / vals_in.  On return keys_out/vals_out (caller buffers of n) hold the sorted pairs. */
-int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, uint64_t* keys_out, uint32_t* vals_out, void* stream);
+/* Stable LSD radix sort of n (u32 key, u32 value) pairs on key bits [0,end_bit), the sort both binning sorts
+ * run on.  scratch = sb200_binning_bytes(n) bytes whose tile ids A / surfel ids A arrays (see layout) hold the
+ * input keys / values and are clobbered.  vals_out (caller buffer of n) receives the values in sorted order.
+ * mode bit 0: 2048-pair tiles instead of 4096.  mode bit 1: the surfel-sort form - values are the indices 0..n-1,
+ * keys equal to 0xFFFFFFFF are dropped, *n_valid_dev (device u32) receives the number of pairs kept. */
+int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, int mode, uint32_t* vals_out, uint32_t* n_valid_dev,
+                     void* stream);
 
 #ifdef __cplusplus
 }

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 15
     for n in sorted(names):
         assert hasattr(lib, n), n
-    assert lib.sb200_abi_version() == 4
+    assert lib.sb200_abi_version() == 5
     assert lib.sb200_last_error() == b""
 
 
@@ -35,7 +35,7 @@ def test_workspace_queries_need_no_gpu():
     prev = 0
     for P in (1, 255, 256, 257, 10_000, 1_200_000, 5_000_000):
         b = lib.sb200_geom_bytes(P)
-        assert b >= prev and b >= 128 * P + 20 * P   # 128-B record + depth/rect/tiles/offsets per surfel
+        assert b >= prev and b >= 128 * P + 32 * P   # 128-B record + depth/rect/tiles + 2 x (key, id) per surfel
         prev = b
         off = (ctypes.c_size_t * 5)()
         lib.sb200_geom_layout(P, off)
@@ -50,7 +50,7 @@ def test_workspace_queries_need_no_gpu():
     assert lib.sb200_image_bytes(1241, 376) >= io[2] + 8 * 1241 * 376
     bo = (ctypes.c_size_t * 4)()
     lib.sb200_binning_layout(1000, bo)
-    assert bo[1] - bo[0] >= 8000 and bo[3] - bo[2] >= 4000
+    assert bo[1] - bo[0] >= 4000 and bo[3] - bo[2] >= 4000
 
 
 def test_bad_arguments_return_errors_not_exceptions():

@@ -22,42 +22,65 @@ def mine():
     return util.load_mine()
 
 
-def _sort(lib, keys, vals, end_bit):
+def _sort(lib, keys, vals, end_bit, mode=0):
+    """keys int64 holding u32 values; vals None = the surfel-sort form (implicit indices, 0xFFFFFFFF keys dropped)"""
     n = keys.numel()
     ws = torch.zeros(max(lib.sb200_binning_bytes(n), 16), dtype=torch.uint8, device="cuda")
     off = (ctypes.c_size_t * 4)()
     lib.sb200_binning_layout(n, off)
     if n:
-        ws[off[0]:off[0] + 8 * n].view(torch.int64).copy_(keys)
-        ws[off[2]:off[2] + 4 * n].view(torch.int32).copy_(vals)
-    ko = torch.zeros(max(n, 1), dtype=torch.int64, device="cuda")
-    vo = torch.zeros(max(n, 1), dtype=torch.int32, device="cuda")
-    rc = lib.sb200_sort_pairs(vp(ws.data_ptr()), n, end_bit, vp(ko.data_ptr()), vp(vo.data_ptr()),
-                              vp(torch.cuda.current_stream().cuda_stream))
+        ws[off[0]:off[0] + 4 * n].view(torch.int32).copy_(keys.to(torch.int32) if keys.dtype != torch.int32 else keys)
+        if vals is not None:
+            ws[off[2]:off[2] + 4 * n].view(torch.int32).copy_(vals)
+    vo = torch.full((max(n, 1),), -1, dtype=torch.int32, device="cuda")
+    nv = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rc = lib.sb200_sort_pairs(vp(ws.data_ptr()), n, end_bit, mode | (2 if vals is None else 0), vp(vo.data_ptr()),
+                              vp(nv.data_ptr()), vp(torch.cuda.current_stream().cuda_stream))
     assert rc == 0, lib.sb200_last_error()
     torch.cuda.synchronize()
-    return ko[:n], vo[:n]
+    return vo[:n], int(nv[0])
 
 
-@pytest.mark.parametrize("n", [0, 1, 31, 4095, 4096, 4097, 100_000, 3_000_001])
-@pytest.mark.parametrize("end_bit", [41, 46, 64])
-def test_radix_sort_is_a_stable_lsd_sort(mine, n, end_bit):
-    """Same contract as cub::DeviceRadixSort::SortPairs(bits [0,end_bit)) at rasterizer_impl.cu:410-418:
-    stable, only the low end_bit bits participate."""
+def _u32_as_i32(x):
+    """int64 tensor of values < 2^32 -> the int32 tensor with the same bits"""
+    return torch.where(x >= (1 << 31), x - (1 << 32), x).to(torch.int32)
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 2047, 2048, 4095, 4096, 4097, 100_000, 3_000_001])
+@pytest.mark.parametrize("end_bit,small", [(1, 0), (8, 1), (11, 0), (13, 0), (16, 1), (17, 0), (32, 1), (32, 0)])
+def test_radix_sort_is_a_stable_lsd_sort(mine, n, end_bit, small):
+    """Same contract as cub::DeviceRadixSort::SortPairs(bits [0,end_bit)) at rasterizer_impl.cu:410-418, on the 32-bit
+    keys this pipeline sorts (tile ids: 11-16 bits in 2 passes; depth words: 32 bits in 4): stable, only the low
+    end_bit bits participate."""
     lib = mine._load()
     gen = torch.Generator(device="cpu").manual_seed(n + end_bit)
-    # few distinct tiles and many duplicated depth words -> long runs of equal keys exercise stability
-    tile = torch.randint(0, 1 << (end_bit - 32) if end_bit < 63 else 1 << 20, (n,), generator=gen, dtype=torch.int64)
-    depth = torch.randint(0, 1 << 12, (n,), generator=gen, dtype=torch.int64) << 19
-    junk = torch.randint(0, 1 << 10, (n,), generator=gen, dtype=torch.int64) << 50 if end_bit < 50 else 0
-    keys = ((tile << 32) | depth | junk).cuda()
+    # few distinct values -> long runs of equal keys exercise stability; junk above end_bit must be ignored
+    lo = torch.randint(0, 1 << min(end_bit, 9), (n,), generator=gen, dtype=torch.int64) << max(0, end_bit - 9)
+    junk = torch.randint(0, 1 << 6, (n,), generator=gen, dtype=torch.int64) << end_bit if end_bit <= 26 else 0
+    keys = lo | junk
     vals = torch.arange(n, dtype=torch.int32, device="cuda")
-    ko, vo = _sort(lib, keys, vals, end_bit)
-    mask = (1 << end_bit) - 1 if end_bit < 64 else -1
-    masked = keys & mask if end_bit < 63 else keys
-    want_k, order = torch.sort(masked, stable=True)
-    assert torch.equal(vo.long(), order)
-    assert torch.equal(ko & mask if end_bit < 63 else ko, want_k)
+    vo, _ = _sort(lib, _u32_as_i32(keys).cuda(), vals, end_bit, mode=small)
+    masked = keys & ((1 << end_bit) - 1)
+    _, order = torch.sort(masked, stable=True)
+    assert torch.equal(vo.long().cpu(), order)
+
+
+@pytest.mark.parametrize("n,frac", [(1, 0.0), (1, 1.0), (2048, 0.5), (5000, 1.0), (300_000, 0.6), (1_200_000, 0.59),
+                                    (1_200_000, 0.999)])
+def test_surfel_sort_drops_invisible_and_keeps_index_order_on_ties(mine, n, frac):
+    """The first pass of the surfel sort compacts: keys 0xFFFFFFFF (surfels touching no tile) vanish, the rest come
+    out as indices in stable (depth word, index) order."""
+    lib = mine._load()
+    gen = torch.Generator(device="cpu").manual_seed(n)
+    depth = (0.2 + 80 * torch.rand(n, generator=gen)).view(torch.int32).long()
+    depth[torch.rand(n, generator=gen) < 0.3] = depth[0]          # many exact ties
+    dead = torch.rand(n, generator=gen) < frac
+    keys = torch.where(dead, torch.full_like(depth, 0xFFFFFFFF), depth)
+    vo, kept = _sort(lib, _u32_as_i32(keys).cuda(), None, 32, mode=1)
+    live = torch.nonzero(~dead).squeeze(1)
+    assert kept == live.numel()
+    _, o = torch.sort(depth[live], stable=True)
+    assert torch.equal(vo[:kept].long().cpu(), live[o])
 
 
 def test_adam_matches_reference_kernel(mine):
@@ -173,7 +196,19 @@ def test_full_size_properties(mine, name):
     mi = util.mine_intermediates(mine, inp)
     R = mi["R"]
     assert R == int(mi["tiles_touched"].sum()) and R > 0
-    assert np.array_equal(mi["offsets"], np.cumsum(mi["tiles_touched"], dtype=np.uint64).astype(np.uint32))
+    # the surfel order is the stable (depth word, id) order of the visible surfels; pairs are emitted in that order,
+    # row-major over each surfel's tile rect
+    vis_ids = np.nonzero(mi["radii"] > 0)[0]
+    dbits = mi["depths"].view(np.uint32)
+    want = vis_ids[np.argsort(dbits[vis_ids], kind="stable")]
+    assert np.array_equal(mi["surfel_order"], want.astype(np.uint32))
+    assert np.array_equal(mi["emitted_ids"], np.repeat(want, mi["tiles_touched"][want]).astype(np.uint32))
+    starts = np.cumsum(mi["tiles_touched"][want].astype(np.int64)) - mi["tiles_touched"][want]
+    gx = (W + 15) // 16
+    for k in np.linspace(0, len(want) - 1, 200).astype(np.int64):
+        r = mi["rect"][want[k]].astype(np.int64)
+        tiles = (np.arange(r[1], r[3])[:, None] * gx + np.arange(r[0], r[2])[None, :]).reshape(-1)
+        assert np.array_equal(mi["emitted_tiles"][starts[k]:starts[k] + len(tiles)].astype(np.int64), tiles)
     # rect area == tiles_touched, radius > 0 <=> touches tiles
     rect = mi["rect"].astype(np.int64)
     area = (rect[:, 2] - rect[:, 0]) * (rect[:, 3] - rect[:, 1])

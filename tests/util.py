@@ -167,19 +167,26 @@ def mine_intermediates(mine, inp):
     rec = fb(g, go[0], 128 * P, np.float32).reshape(P, 32)  # 8 quads, layout in csrc/common.cuh
     N = W * H
     tiles_n = ((W + 15) // 16) * ((H + 15) // 16)
-    passes = (32 + _higher_msb(tiles_n) + 7) // 8
-    # after an even number of passes the sorted keys are back in buffer A, else in B
-    keys_sorted = fb(b, bo[0] if passes % 2 == 0 else bo[1], 8 * R, np.uint64)
+    ranges = fb(im, io[0], 8 * tiles_n, np.uint32).reshape(tiles_n, 2)
+    depths = fb(g, go[1], 4 * P, np.float32)
+    pl = point_list.cpu().numpy()[:R].view(np.uint32)
+    # the reference's sorted 64-bit keys, restated from what this pipeline keeps: the tile of a list position comes
+    # from the ranges, the depth word from the surfel at that position
+    tile_of = np.zeros(R, dtype=np.uint64)
+    for t in np.nonzero(ranges[:, 1] > ranges[:, 0])[0]:
+        tile_of[ranges[t, 0]:ranges[t, 1]] = t
+    keys_sorted = (tile_of << np.uint64(32)) | depths.view(np.uint32)[pl].astype(np.uint64)
+    V = int((radii > 0).sum())
     vis = radii.cpu().numpy() > 0
     return dict(R=R, color=color.cpu(), allmap=others.cpu(), radii=radii.cpu().numpy(), visible=vis,
-                depths=fb(g, go[1], 4 * P, np.float32), rect=fb(g, go[2], 8 * P, np.uint16).reshape(P, 4),
-                tiles_touched=fb(g, go[3], 4 * P, np.uint32), offsets=fb(g, go[4], 4 * P, np.uint32),
+                depths=depths, rect=fb(g, go[2], 8 * P, np.uint16).reshape(P, 4),
+                tiles_touched=fb(g, go[3], 4 * P, np.uint32), surfel_order=fb(g, go[4], 4 * P, np.uint32)[:V],
+                emitted_tiles=fb(b, bo[0], 4 * R, np.uint32), emitted_ids=fb(b, bo[2], 4 * R, np.uint32),
                 means2D=np.stack([rec[:, 3], rec[:, 7]], -1),
                 transMat=np.concatenate([rec[:, 12:15], rec[:, 16:19], rec[:, 20:23]], -1),
                 normal_opacity=np.concatenate([rec[:, 24:27], rec[:, 15:16]], -1),
                 cull_tau=rec[:, 11], bbox=rec[:, 28:32],
-                keys=keys_sorted, point_list=point_list.cpu().numpy()[:R].view(np.uint32),
-                ranges=fb(im, io[0], 8 * tiles_n, np.uint32).reshape(tiles_n, 2),
+                keys=keys_sorted, point_list=pl, ranges=ranges,
                 final_T=fb(im, io[1], 12 * N, np.float32).reshape(3, N),
                 n_contrib=fb(im, io[2], 8 * N, np.uint32).reshape(2, N))
 

@@ -55,7 +55,7 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 4; }
+int sb200_abi_version(void) { return 5; }
 
 long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -90,7 +90,7 @@ size_t sb200_grad_bytes(int64_t P) { return sb_align((size_t)(P > 0 ? P : 0) * S
 
 void sb200_geom_layout(int64_t P, size_t out[5]) {
     SbGeomLayout L = sb_geom_layout(P);
-    out[0] = L.rec; out[1] = L.depth; out[2] = L.rect; out[3] = L.tiles; out[4] = L.offsets;
+    out[0] = L.rec; out[1] = L.depth; out[2] = L.rect; out[3] = L.tiles; out[4] = L.sort_v[1];
 }
 void sb200_image_layout(int W, int H, size_t out[3]) {
     SbImageLayout L = sb_image_layout(W, H);
@@ -99,6 +99,16 @@ void sb200_image_layout(int W, int H, size_t out[3]) {
 void sb200_binning_layout(int64_t R, size_t out[4]) {
     SbBinLayout L = sb_bin_layout(R);
     out[0] = L.keys_a; out[1] = L.keys_b; out[2] = L.vals_a; out[3] = L.vals_b;
+}
+
+// One event per (thread, device): lets forward_begin wait for the read-back of R alone while the surfel sort,
+// queued behind it on the same stream, keeps the GPU busy.
+static cudaEvent_t sync_event() {
+    thread_local cudaEvent_t ev[64] = {};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    if (!ev[dev] && cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming) != cudaSuccess) ev[dev] = nullptr;
+    return ev[dev];
 }
 
 static int check_dims(int P, int W, int H) {
@@ -131,10 +141,16 @@ int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* 
     }
     if (rc) return rc;
     SbGeomLayout L = sb_geom_layout(P);
-    const int nblocks = (P + 255) / 256;
-    const unsigned long long* total = (const unsigned long long*)((char*)geom_ws + L.scan_state) + nblocks + 1;
-    SB_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, total, 8, cudaMemcpyDeviceToHost, s));
-    SB_CUDA_CHECK(cudaStreamSynchronize(s));
+    cudaEvent_t ev = sync_event();
+    SB_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, (char*)geom_ws + L.counts, 8, cudaMemcpyDeviceToHost, s));
+    if (ev) SB_CUDA_CHECK(cudaEventRecord(ev, s));
+    {
+        StageScope sc(SB200_STAGE_SURFEL_SORT, s);
+        rc = sb_launch_surfel_sort(P, (char*)geom_ws, s);
+    }
+    if (rc) return rc;
+    if (ev) SB_CUDA_CHECK(cudaEventSynchronize(ev));
+    else SB_CUDA_CHECK(cudaStreamSynchronize(s));
     return 0;
 }
 
@@ -147,33 +163,42 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
     cudaStream_t s = (cudaStream_t)stream;
     const int tiles = ((W + SB_TILE_X - 1) / SB_TILE_X) * ((H + SB_TILE_Y - 1) / SB_TILE_Y);
     SbImageLayout IL = sb_image_layout(W, H);
-    uint64_t* keys_sorted = nullptr;
+    uint32_t* tile_counts = (uint32_t*)((char*)image_ws + IL.counts);
+    uint2* ranges = (uint2*)((char*)image_ws + IL.ranges);
+    uint32_t* order = (uint32_t*)((char*)image_ws + IL.order);
+    const SbSortPlan pl = sb_sort_plan((int)sb_higher_msb((uint32_t)tiles));  // the reference's tile bit count (:410)
     int rc;
+    SB_CUDA_CHECK(cudaMemsetAsync(tile_counts, 0, (size_t)tiles * 4, s));
     if (R > 0) {
         SbBinLayout BL = sb_bin_layout(R);
         char* bw = (char*)binning_ws;
-        uint64_t* keys_a = (uint64_t*)(bw + BL.keys_a);
-        uint64_t* keys_b = (uint64_t*)(bw + BL.keys_b);
-        uint32_t* vals_a = (uint32_t*)(bw + BL.vals_a);
-        uint32_t* vals_b = (uint32_t*)(bw + BL.vals_b);
+        uint32_t* kbuf[2] = {(uint32_t*)(bw + BL.keys_b), (uint32_t*)(bw + BL.keys_a)};
+        uint32_t* vbuf[2] = {(uint32_t*)(bw + BL.vals_b), (uint32_t*)(bw + BL.vals_a)};
+        SB_CUDA_CHECK(cudaMemsetAsync(bw + BL.zero_begin, 0,
+                                      (BL.status - BL.zero_begin) + sb_sort_status_bytes(R, pl.passes, 0), s));
         {
             StageScope sc(SB200_STAGE_DUPLICATE, s);
-            rc = sb_launch_duplicate(P, W, H, (const char*)geom_ws, keys_a, vals_a, s);
+            rc = sb_launch_duplicate(P, W, H, R, (const char*)geom_ws, (uint32_t*)(bw + BL.chunk_first), tile_counts,
+                                     kbuf[1], vbuf[1], s);
         }
         if (rc) return rc;
-        const int end_bit = 32 + (int)sb_higher_msb((uint32_t)tiles);
+        {
+            StageScope sc(SB200_STAGE_RANGES, s);
+            rc = sb_launch_tile_scan(tiles, pl, tile_counts, ranges, order, (uint32_t*)(bw + BL.hist), s);
+        }
+        if (rc) return rc;
         {
             StageScope sc(SB200_STAGE_SORT, s);
-            rc = sb_launch_sort_pairs(keys_a, vals_a, keys_b, vals_b, &keys_sorted, point_list, R, end_bit, bw, BL, s);
+            rc = sb_launch_sort_passes(pl, 0, kbuf[1], vbuf[1], kbuf, vbuf, point_list, R, nullptr,
+                                       (const uint32_t*)(bw + BL.hist), (uint32_t*)(bw + BL.tickets),
+                                       (uint32_t*)(bw + BL.status), s);
         }
         if (rc) return rc;
-    }
-    {
+    } else {
         StageScope sc(SB200_STAGE_RANGES, s);
-        rc = sb_launch_tile_ranges(R, tiles, keys_sorted, (uint2*)((char*)image_ws + IL.ranges),
-                                   (uint32_t*)((char*)image_ws + IL.order), s);
+        rc = sb_launch_tile_scan(tiles, pl, tile_counts, ranges, order, nullptr, s);
+        if (rc) return rc;
     }
-    if (rc) return rc;
     // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does
     StageScope sc(SB200_STAGE_BLEND_FWD, s);
     return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others, s);
@@ -260,18 +285,25 @@ int sb200_activate(int P, const float* opacity_raw, const float* scaling_raw, co
                               (cudaStream_t)stream);
 }
 
-int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, uint64_t* keys_out, uint32_t* vals_out, void* stream) {
+int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, int mode, uint32_t* vals_out, uint32_t* n_valid_dev,
+                     void* stream) {
     g_err[0] = 0;
     if (n <= 0) return 0;
+    if (end_bit < 1 || end_bit > 32) { sb_set_error("sort_pairs: end_bit must be in [1,32]"); return 1; }
+    const int small = mode & 1, drop = (mode >> 1) & 1;
+    if (drop && !n_valid_dev) { sb_set_error("sort_pairs: drop mode needs n_valid_dev"); return 1; }
     cudaStream_t s = (cudaStream_t)stream;
     SbBinLayout BL = sb_bin_layout(n);
     char* bw = (char*)binning_ws;
-    uint64_t* keys_sorted = nullptr;
-    int rc = sb_launch_sort_pairs((uint64_t*)(bw + BL.keys_a), (uint32_t*)(bw + BL.vals_a), (uint64_t*)(bw + BL.keys_b),
-                                  (uint32_t*)(bw + BL.vals_b), &keys_sorted, vals_out, n, end_bit, bw, BL, s);
+    const SbSortPlan pl = sb_sort_plan(end_bit);
+    uint32_t* kbuf[2] = {(uint32_t*)(bw + BL.keys_b), (uint32_t*)(bw + BL.keys_a)};
+    uint32_t* vbuf[2] = {(uint32_t*)(bw + BL.vals_b), (uint32_t*)(bw + BL.vals_a)};
+    SB_CUDA_CHECK(cudaMemsetAsync(bw + BL.hist, 0, (BL.status - BL.hist) + sb_sort_status_bytes(n, pl.passes, small), s));
+    int rc = sb_launch_sort_hist(kbuf[1], n, pl, drop, (uint32_t*)(bw + BL.hist), n_valid_dev, s);
     if (rc) return rc;
-    SB_CUDA_CHECK(cudaMemcpyAsync(keys_out, keys_sorted, (size_t)n * 8, cudaMemcpyDeviceToDevice, s));
-    return 0;
+    return sb_launch_sort_passes(pl, small, kbuf[1], drop ? nullptr : vbuf[1], kbuf, vbuf, vals_out, n,
+                                 drop ? n_valid_dev : nullptr, (const uint32_t*)(bw + BL.hist),
+                                 (uint32_t*)(bw + BL.tickets), (uint32_t*)(bw + BL.status), s);
 }
 
 }  // extern "C"

@@ -44,14 +44,35 @@
 
 static inline __host__ __device__ size_t sb_align(size_t x, size_t a = 256) { return (x + a - 1) / a * a; }
 
+// Radix sort geometry (onesweep).
+#define SB_SORT_THREADS 256
+#define SB_SORT_ITEMS 16        // pair sort: 4096-pair tiles
+#define SB_SORT_ITEMS_SMALL 8   // surfel sort: 2048-surfel tiles (more CTAs for the shorter input)
+#define SB_RADIX_BITS 8
+#define SB_RADIX 256
+#define SB_MAX_PASSES 4
+#define SB_KEY_INVALID 0xffffffffu  // depth key of a surfel that touches no tile: dropped by the surfel sort
+#define SB_DEPTH_BITS 32
+#define SB_EMIT_CHUNK 1024  // pairs per work unit of the duplicate kernel
+
+struct SbSortPlan { int end_bit, passes, width; };
+SbSortPlan sb_sort_plan(int end_bit);
+
 // Geometry workspace (caller-allocated, P-sized). Offsets in bytes.
 struct SbGeomLayout {
-    size_t rec;        // float4[5P]
-    size_t depth;      // float[P]       view-space z (key low word)
+    size_t rec;        // float4[8P]
+    size_t depth;      // float[P]       view-space z of the visible surfels
     size_t rect;       // ushort4[P]     tile rect (min.x, min.y, max.x, max.y)
     size_t tiles;      // uint32[P]      tiles_touched
-    size_t offsets;    // uint32[P]      inclusive prefix sum of tiles_touched
-    size_t scan_state; // uint64[nblk+2] look-back status words + ticket + total
+    size_t sort_k[2];  // uint32[P] x 2  depth keys: [1] is written by preprocess (SB_KEY_INVALID = not visible)
+    size_t sort_v[2];  // uint32[P] x 2  surfel ids; after the 4 passes [1] holds the V visible ids in depth order
+    size_t state;      // zeroed before every forward:
+    size_t hist;       //   uint32[4*256]  digit bases of the surfel sort
+    size_t tickets;    //   uint32[8]      [0..3] sort pass tickets, [4] duplicate ticket
+    size_t counts;     //   uint64[2]      [0] R = sum of tiles_touched, [1] (low word) V = visible surfels
+    size_t dup_state;  //   uint64[ceil(P/256)]  look-back words of the pair-offset scan
+    size_t status;     //   uint32[4 * ceil(P/2048) * 256]  look-back words of the surfel sort
+    size_t state_bytes;
     size_t total;
 };
 
@@ -63,8 +84,16 @@ static inline __host__ SbGeomLayout sb_geom_layout(int64_t P) {
     L.depth = o;      o = sb_align(o + p * 4);
     L.rect = o;       o = sb_align(o + p * 8);
     L.tiles = o;      o = sb_align(o + p * 4);
-    L.offsets = o;    o = sb_align(o + p * 4);
-    L.scan_state = o; o = sb_align(o + ((p + 255) / 256 + 4) * 8);
+    for (int i = 0; i < 2; i++) { L.sort_k[i] = o; o = sb_align(o + p * 4); }
+    for (int i = 0; i < 2; i++) { L.sort_v[i] = o; o = sb_align(o + p * 4); }
+    L.state = o;
+    L.hist = o;       o = sb_align(o + SB_MAX_PASSES * SB_RADIX * 4);
+    L.tickets = o;    o = sb_align(o + 8 * 4);
+    L.counts = o;     o = sb_align(o + 2 * 8);
+    L.dup_state = o;  o = sb_align(o + ((p + 255) / 256 + 1) * 8);
+    size_t nt = (p + SB_SORT_THREADS * SB_SORT_ITEMS_SMALL - 1) / (SB_SORT_THREADS * SB_SORT_ITEMS_SMALL);
+    L.status = o;     o = sb_align(o + (size_t)SB_MAX_PASSES * nt * SB_RADIX * 4);
+    L.state_bytes = o - L.state;
     L.total = o;
     return L;
 }
@@ -75,6 +104,7 @@ struct SbImageLayout {
     size_t final_T;   // float[3*HW]   T, M1, M2   (reference: ImageState::accum_alpha)
     size_t n_contrib; // uint32[2*HW]  last contributor, median contributor
     size_t order;     // uint32[tiles] launch order of the tiles, longest list first
+    size_t counts;    // uint32[tiles] pairs per tile, accumulated by the duplicate kernel
     size_t total;
 };
 
@@ -87,41 +117,36 @@ static inline __host__ SbImageLayout sb_image_layout(int W, int H) {
     L.final_T = o;   o = sb_align(o + hw * 12);
     L.n_contrib = o; o = sb_align(o + hw * 8);
     L.order = o;     o = sb_align(o + tiles * 4);
+    L.counts = o;    o = sb_align(o + tiles * 4);
     L.total = o;
     return L;
 }
 
-// Radix sort geometry (onesweep).
-#define SB_SORT_THREADS 256
-#define SB_SORT_ITEMS 16
-#define SB_SORT_TILE (SB_SORT_THREADS * SB_SORT_ITEMS)
-#define SB_RADIX_BITS 8
-#define SB_RADIX 256
-#define SB_MAX_PASSES 8
-
 // Binning scratch (caller-allocated, R-sized; only point_list survives the forward and it is a
 // separate caller buffer).
 struct SbBinLayout {
-    size_t keys_a, keys_b;  // uint64[R]
-    size_t vals_a, vals_b;  // uint32[R]
-    size_t hist;            // uint32[SB_MAX_PASSES*256] global digit histograms -> exclusive bases
+    size_t keys_a, keys_b;  // uint32[R]  tile id of every pair
+    size_t vals_a, vals_b;  // uint32[R]  surfel id of every pair
+    size_t chunk_first;     // uint32[ceil(R/1024)] depth-order index of the surfel owning each chunk's first pair
+    size_t hist;            // uint32[SB_MAX_PASSES*256] exclusive digit bases of the pair sort (tile-count scan)
     size_t tickets;         // uint32[SB_MAX_PASSES]
     size_t status;          // uint32[passes * ntiles * 256] look-back words
-    size_t zero_begin, zero_bytes; // the region that must be zeroed before a sort
+    size_t zero_begin, zero_bytes; // tickets + status; a sort zeroes tickets + the status words it will use
     size_t total;
 };
 
 static inline __host__ SbBinLayout sb_bin_layout(int64_t R) {
     SbBinLayout L;
     size_t r = (size_t)(R > 0 ? R : 0);
-    size_t ntiles = (r + SB_SORT_TILE - 1) / SB_SORT_TILE;
+    size_t ntiles = (r + SB_SORT_THREADS * SB_SORT_ITEMS_SMALL - 1) / (SB_SORT_THREADS * SB_SORT_ITEMS_SMALL);
     size_t o = 0;
-    L.keys_a = o; o = sb_align(o + r * 8);
-    L.keys_b = o; o = sb_align(o + r * 8);
+    L.keys_a = o; o = sb_align(o + r * 4);
+    L.keys_b = o; o = sb_align(o + r * 4);
     L.vals_a = o; o = sb_align(o + r * 4);
     L.vals_b = o; o = sb_align(o + r * 4);
-    L.zero_begin = o;
+    L.chunk_first = o; o = sb_align(o + ((r + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK + 1) * 4);
     L.hist = o;    o = sb_align(o + SB_MAX_PASSES * SB_RADIX * 4);
+    L.zero_begin = o;
     L.tickets = o; o = sb_align(o + SB_MAX_PASSES * 4);
     L.status = o;  o = sb_align(o + (size_t)SB_MAX_PASSES * ntiles * SB_RADIX * 4);
     L.zero_bytes = o - L.zero_begin;
@@ -131,6 +156,12 @@ static inline __host__ SbBinLayout sb_bin_layout(int64_t R) {
 
 // Same bit count the reference passes to its sort: 32 + getHigherMsb(tiles)
 // (DSR/cuda_rasterizer/rasterizer_impl.cu:35-50,410).
+// bytes from BinLayout::zero_begin (or GeomLayout::tickets ...) a sort of n pairs in `passes` passes must find zeroed
+static inline __host__ size_t sb_sort_status_bytes(int64_t n, int passes, int small) {
+    size_t tile = (size_t)SB_SORT_THREADS * (small ? SB_SORT_ITEMS_SMALL : SB_SORT_ITEMS);
+    return (size_t)passes * (((size_t)(n > 0 ? n : 0) + tile - 1) / tile) * SB_RADIX * 4;
+}
+
 static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
     uint32_t msb = sizeof(n) * 4;
     uint32_t step = msb;
@@ -164,12 +195,17 @@ int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float*
                          const float* opacities, const float* colors, const float* viewmatrix,
                          const float* projmatrix, char* geom, int* radii, cudaStream_t s);
 int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
-int sb_launch_duplicate(int P, int W, int H, const char* geom, uint64_t* keys, uint32_t* vals, cudaStream_t s);
-int sb_launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_tmp, uint32_t* vals_tmp,
-                         uint64_t** keys_sorted, uint32_t* vals_final, int64_t n, int end_bit, char* bin_base,
-                         const SbBinLayout& L, cudaStream_t s);
-int sb_launch_tile_ranges(int64_t R, int tiles, const uint64_t* keys_sorted, uint2* ranges, uint32_t* order,
+int sb_launch_surfel_sort(int P, char* geom, cudaStream_t s);
+int sb_launch_duplicate(int P, int W, int H, int64_t R, const char* geom, uint32_t* chunk_first, uint32_t* tile_counts,
+                        uint32_t* keys, uint32_t* vals, cudaStream_t s);
+int sb_launch_sort_hist(const uint32_t* keys, int64_t n, const SbSortPlan& pl, int drop_invalid, uint32_t* digit_base,
+                        uint32_t* n_valid, cudaStream_t s);
+int sb_launch_sort_passes(const SbSortPlan& pl, int small, const uint32_t* keys_in, const uint32_t* vals_in,
+                          uint32_t* const kbuf[2], uint32_t* const vbuf[2], uint32_t* vals_final, int64_t n,
+                          const uint32_t* n_dev, const uint32_t* digit_base, uint32_t* tickets, uint32_t* status,
                           cudaStream_t s);
+int sb_launch_tile_scan(int tiles, const SbSortPlan& pl, const uint32_t* tile_counts, uint2* ranges, uint32_t* order,
+                        uint32_t* digit_base, cudaStream_t s);
 int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                             char* image, float* out_color, float* out_others, cudaStream_t s);
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,

@@ -1,18 +1,15 @@
-// K1: per-surfel forward preprocess fused with the tiles_touched prefix sum, plus mark_visible.
+// K1: per-surfel forward preprocess, the depth-ordered surfel list, plus mark_visible.
 //
-// Replaces DSR/cuda_rasterizer/forward.cu:160-249 (preprocessCUDA), the cub::DeviceScan call at
-// rasterizer_impl.cu:387 and checkFrustum (rasterizer_impl.cu:106-118).  One thread per surfel,
-// 256 surfels per CTA.  The [P,3] inputs are staged through shared memory with 128-bit coalesced
-// loads; rotations are natural float4s.  Each CTA publishes its tile-count aggregate and resolves
-// its exclusive prefix by decoupled look-back, so offsets are written by the same kernel.
+// Replaces DSR/cuda_rasterizer/forward.cu:160-249 (preprocessCUDA) and checkFrustum (rasterizer_impl.cu:106-118).
+// One thread per surfel, 256 surfels per CTA.  The [P,3] inputs are staged through shared memory with 128-bit
+// coalesced loads; rotations are natural float4s.  Besides the render record the kernel writes the surfel's
+// sort key (its depth word, SB_KEY_INVALID when it touches no tile) and adds its tile count to R; the
+// reference's prefix sum over tiles_touched (cub::DeviceScan, rasterizer_impl.cu:387) moves into the duplicate
+// kernel because pairs are emitted in depth order here (radix_sort.cu).
 #include "surfel_math.cuh"
 #include "surfel_math_pinned.cuh"
 
 #define PRE_THREADS 256
-
-// look-back status word: [63:62] flag (1 = aggregate, 2 = inclusive prefix), [31:0] value
-#define SCAN_FLAG_AGG (1ull << 62)
-#define SCAN_FLAG_INC (2ull << 62)
 
 // Cooperative 128-bit load of `n3` consecutive floats starting at src (16-B aligned) into smem.
 __device__ __forceinline__ void sb_stage_f3(float* dst, const float* __restrict__ src, int nfloats, bool aligned) {
@@ -33,22 +30,16 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
                      const float* __restrict__ colors, const float* __restrict__ viewmatrix,
                      const float* __restrict__ projmatrix, float4* __restrict__ rec, float* __restrict__ depths,
                      ushort4* __restrict__ rects, uint32_t* __restrict__ tiles_touched,
-                     uint32_t* __restrict__ offsets, unsigned long long* __restrict__ scan_state,
-                     int* __restrict__ radii, int nblocks) {
+                     uint32_t* __restrict__ sort_keys, unsigned long long* __restrict__ total_pairs,
+                     int* __restrict__ radii) {
     __shared__ __align__(16) float s_mean[PRE_THREADS * 3];
     __shared__ __align__(16) float s_col[PRE_THREADS * 3];
     __shared__ float s_vm[16], s_pm[16];
     __shared__ uint32_t s_warp[PRE_THREADS / 32];
-    __shared__ uint32_t s_blk, s_prefix;
 
-    // ticket = logical block index; guarantees every predecessor has started (look-back progress)
-    unsigned long long* ticket = scan_state + nblocks;
-    if (threadIdx.x == 0) s_blk = (uint32_t)atomicAdd(ticket, 1ull);
     if (threadIdx.x < 16) s_vm[threadIdx.x] = viewmatrix[threadIdx.x];
     else if (threadIdx.x < 32) s_pm[threadIdx.x - 16] = projmatrix[threadIdx.x - 16];
-    __syncthreads();
-    const uint32_t blk = s_blk;
-    const int base = blk * PRE_THREADS;
+    const int base = blockIdx.x * PRE_THREADS;
     const int n_here = min(PRE_THREADS, P - base);
     const bool al = ((((uintptr_t)(means3D + (size_t)base * 3)) | ((uintptr_t)(colors + (size_t)base * 3))) & 15) == 0;
     sb_stage_f3(s_mean, means3D + (size_t)base * 3, n_here * 3, al);
@@ -59,6 +50,7 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
     uint32_t touched = 0;
     if (idx < P) {
         int radius_i = 0;
+        uint32_t sort_key = SB_KEY_INVALID;
         float3 p_orig = {s_mean[3 * threadIdx.x], s_mean[3 * threadIdx.x + 1], s_mean[3 * threadIdx.x + 2]};
         // near cull only (auxiliary.h:197-222); p_hom/p_proj of the reference are dead code
         // operation order of the oracle build (FMUL on the m6*y term, auxiliary.h:91-99 as nvcc contracts it)
@@ -82,6 +74,7 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
                     touched = area;
                     radius_i = (int)radius;
                     depths[idx] = pz;
+                    sort_key = __float_as_uint(pz);
                     rects[idx] = make_ushort4((unsigned short)rmin.x, (unsigned short)rmin.y,
                                               (unsigned short)rmax.x, (unsigned short)rmax.y);
                     const float opa = __ldg(opacities + idx);
@@ -103,72 +96,20 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
         }
         radii[idx] = radius_i;
         tiles_touched[idx] = touched;
+        sort_keys[idx] = sort_key;
     }
 
-    // ---- block inclusive scan of `touched` ----
+    // ---- R += this CTA's pairs (one atomic per CTA) ----
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    uint32_t incl = touched;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    if (lane == 31) s_warp[wid] = incl;
+    const uint32_t wsum = __reduce_add_sync(0xffffffffu, touched);
+    if (lane == 0) s_warp[wid] = wsum;
     __syncthreads();
-    if (wid == 0) {
-        uint32_t w = (lane < PRE_THREADS / 32) ? s_warp[lane] : 0;
+    if (threadIdx.x == 0) {
+        unsigned long long t = 0;
 #pragma unroll
-        for (int o = 1; o < PRE_THREADS / 32; o <<= 1) {
-            uint32_t v = __shfl_up_sync(0xffffffffu, w, o);
-            if (lane >= o) w += v;
-        }
-        if (lane < PRE_THREADS / 32) s_warp[lane] = w;  // inclusive over warps
+        for (int w = 0; w < PRE_THREADS / 32; w++) t += s_warp[w];
+        if (t) atomicAdd(total_pairs, t);
     }
-    __syncthreads();
-    const uint32_t block_total = s_warp[PRE_THREADS / 32 - 1];
-    const uint32_t warp_excl = wid ? s_warp[wid - 1] : 0;
-
-    // ---- decoupled look-back across CTAs (one warp) ----
-    if (wid == 0) {
-        volatile unsigned long long* st = scan_state;
-        if (lane == 0) {
-            unsigned long long word = (blk == 0 ? SCAN_FLAG_INC : SCAN_FLAG_AGG) | block_total;
-            st[blk] = word;
-        }
-        uint32_t prefix = 0;
-        if (blk > 0) {
-            int look = (int)blk - 1 - lane;  // each lane inspects one predecessor per round
-            while (true) {
-                unsigned long long w = 0;
-                if (look >= 0) {
-                    do { w = st[look]; } while ((w >> 62) == 0);
-                } else {
-                    w = SCAN_FLAG_INC;  // virtual predecessor before block 0
-                }
-                unsigned inc_mask = __ballot_sync(0xffffffffu, (w >> 62) == 2);
-                uint32_t val = (uint32_t)w;
-                if (inc_mask) {
-                    int first = __ffs(inc_mask) - 1;  // nearest predecessor holding an inclusive prefix
-                    if (lane > first) val = 0;
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) val += __shfl_xor_sync(0xffffffffu, val, o);
-                prefix += val;
-                if (inc_mask) break;
-                look -= 32;
-            }
-            if (lane == 0) {
-                __threadfence();
-                st[blk] = SCAN_FLAG_INC | (unsigned long long)(prefix + block_total);
-            }
-        }
-        if (lane == 0) {
-            s_prefix = prefix;
-            if (blk == (uint32_t)nblocks - 1) scan_state[nblocks + 1] = (unsigned long long)prefix + block_total;  // R
-        }
-    }
-    __syncthreads();
-    if (idx < P) offsets[idx] = s_prefix + warp_excl + incl;
 }
 
 __global__ void sb_mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ vm,
@@ -185,15 +126,30 @@ int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float*
                          const float* projmatrix, char* geom, int* radii, cudaStream_t s) {
     SbGeomLayout L = sb_geom_layout(P);
     int nblocks = (P + PRE_THREADS - 1) / PRE_THREADS;
-    SB_CUDA_CHECK(cudaMemsetAsync(geom + L.scan_state, 0, (size_t)(nblocks + 2) * 8, s));
+    SB_CUDA_CHECK(cudaMemsetAsync(geom + L.state, 0, L.state_bytes, s));
     if (P == 0) return 0;
     sb_preprocess_kernel<<<nblocks, PRE_THREADS, 0, s>>>(
         P, W, H, means3D, (const float2*)scales, (const float4*)rotations, opacities, colors, viewmatrix, projmatrix,
         (float4*)(geom + L.rec), (float*)(geom + L.depth), (ushort4*)(geom + L.rect), (uint32_t*)(geom + L.tiles),
-        (uint32_t*)(geom + L.offsets), (unsigned long long*)(geom + L.scan_state), radii, nblocks);
+        (uint32_t*)(geom + L.sort_k[1]), (unsigned long long*)(geom + L.counts), radii);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
+}
+
+// Stable sort of the visible surfels by depth word: geom.sort_v[1][0..V) = their ids, V -> geom.counts[1].
+int sb_launch_surfel_sort(int P, char* geom, cudaStream_t s) {
+    if (P == 0) return 0;
+    SbGeomLayout L = sb_geom_layout(P);
+    const SbSortPlan pl = sb_sort_plan(SB_DEPTH_BITS);
+    uint32_t* kbuf[2] = {(uint32_t*)(geom + L.sort_k[0]), (uint32_t*)(geom + L.sort_k[1])};
+    uint32_t* vbuf[2] = {(uint32_t*)(geom + L.sort_v[0]), (uint32_t*)(geom + L.sort_v[1])};
+    uint32_t* hist = (uint32_t*)(geom + L.hist);
+    uint32_t* n_valid = (uint32_t*)(geom + L.counts + 8);
+    int rc = sb_launch_sort_hist(kbuf[1], P, pl, 1, hist, n_valid, s);
+    if (rc) return rc;
+    return sb_launch_sort_passes(pl, 1, kbuf[1], nullptr, kbuf, vbuf, vbuf[1], P, n_valid, hist,
+                                 (uint32_t*)(geom + L.tickets), (uint32_t*)(geom + L.status), s);
 }
 
 int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s) {

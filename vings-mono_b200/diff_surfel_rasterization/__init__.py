@@ -67,7 +67,7 @@ def _load():
     lib.sb200_adam_update.restype = _i32
     lib.sb200_adam_update.argtypes = [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _u32, _u32, _vp]
     lib.sb200_sort_pairs.restype = _i32
-    lib.sb200_sort_pairs.argtypes = [_vp, _i64, _i32, _vp, _vp, _vp]
+    lib.sb200_sort_pairs.argtypes = [_vp, _i64, _i32, _i32, _vp, _vp, _vp]
     lib.sb200_launch_count.restype = ctypes.c_longlong
     lib.sb200_profile_enable.restype = _i32
     lib.sb200_profile_enable.argtypes = [_i32]
@@ -88,7 +88,7 @@ def _load():
     lib.sb200_prune_scratch_bytes.argtypes = [_i64]
     lib.sb200_prune_rows.restype = _i32
     lib.sb200_prune_rows.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp]
-    if lib.sb200_abi_version() != 4:
+    if lib.sb200_abi_version() != 5:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -130,7 +130,7 @@ def _count_buffer(device):
 
 
 STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam",
-          "map_loss", "activate", "update", "churn")
+          "map_loss", "activate", "update", "churn", "surfel_sort")
 
 
 def profile_enable(on=True):
