@@ -104,6 +104,22 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg /* [3] 
                          void* geom_ws, void* binning_ws, uint32_t* point_list, void* image_ws,
                          float* out_color, float* out_others, void* stream);
 
+/* Both stages in one call WITHOUT a host synchronisation, for callers that keep a binning scratch of
+ * `pair_capacity` pairs (sb200_binning_bytes(pair_capacity), point_list[pair_capacity]): every launch takes the
+ * pair count from device memory.  R is copied to *num_rendered_host (pinned host memory) right after the
+ * preprocess; sb200_forward_wait() blocks until that copy of the calling thread's most recent forward_async on the
+ * current device has landed - call it wherever convenient before committing the view's results (the mapper
+ * does just before its parameter update, with the rest of the view already queued, so the GPU never idles).
+ * If R > pair_capacity only the first pair_capacity pairs (depth order) were binned: the outputs are memory-safe
+ * but wrong, and the caller must grow the scratch and run the forward again.  Pass pair_capacity (not R) as R to
+ * sb200_backward. */
+int sb200_forward_async(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                        const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
+                        const float* bg, void* geom_ws, int* radii, void* binning_ws, int64_t pair_capacity,
+                        uint32_t* point_list, void* image_ws, float* out_color, float* out_others,
+                        int64_t* num_rendered_host, void* stream);
+int sb200_forward_wait(void);
+
 /* ---- backward ------------------------------------------------------------------------------- */
 /* All dL_d* outputs and scores are fully written (no pre-zeroing needed).  dL_dtransMat may be NULL.
  * pixel_mask: u8/bool [H*W]; masked-out pixels contribute no gradient and no score. */

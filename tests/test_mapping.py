@@ -8,6 +8,7 @@ Oracles:
 Tolerances are fp32 rounding: the fused kernels sum in a different association (separable filter, block
 reductions) than torch's conv2d / masked means.
 """
+import ctypes
 import os
 
 import numpy as np
@@ -236,3 +237,50 @@ def test_update_dp_modes_equal_local_on_one_rank():
     for x, y in zip(pa + ma + va + ba, pb + mb + vb + bb):
         assert torch.equal(x, y)
     assert not torch.equal(pa[0], m._xyz.data)
+
+
+@pytest.mark.gpu
+def test_forward_async_is_the_forward_and_survives_a_too_small_scratch():
+    """sb200_forward_async (pair count kept on the device, no host wait inside the forward) gives the bits of the
+    two-stage forward when the kept scratch is large enough; with a scratch that is too small it stays inside its
+    buffers, confirm() reports it and grows the scratch."""
+    mine = util.load_mine()
+    mp = mine.mapping
+    scene, views = synthetic.make_scene("C3", P=60000, W=320, H=192)
+    inp = util.cuda_inputs(synthetic.view_inputs(scene, views[-1]))
+    dev = inp["means3D"].device
+    args = (inp["means3D"], inp["scales"], inp["rotations"], inp["opacities"], inp["colors"], inp["bg"],
+            inp["viewmatrix"], inp["projmatrix"])
+    a = mp.RasterWorkspace(inp["means3D"].shape[0], inp["W"], inp["H"], dev)
+    a.forward(*args)
+    R = a.R
+    io = (ctypes.c_size_t * 3)()
+    mine._load().sb200_image_layout(inp["W"], inp["H"], io)
+    kept = io[2] + 8 * inp["W"] * inp["H"]   # ranges, final T/M1/M2, contributor counts (the launch order is not unique)
+    ref = (a.color.clone(), a.allmap.clone(), a.radii.clone(), a.point_list[:R].clone(), a.image[:kept].clone())
+    assert R > 5000
+    # same workspace again, asynchronously (scratch holds 1.25 R pairs)
+    a.color.zero_(); a.allmap.zero_(); a.point_list.zero_()
+    a.forward_async(*args)
+    assert a.confirm() and mp.last_counters["R"] == R
+    torch.cuda.synchronize()
+    got = (a.color, a.allmap, a.radii, a.point_list[:R], a.image[:kept])
+    for x, y in zip(got, ref):
+        assert torch.equal(x, y)
+    # a scratch of R/3 pairs surrounded by canaries: nothing outside is written, confirm() says no and grows it
+    b = mp.RasterWorkspace(inp["means3D"].shape[0], inp["W"], inp["H"], dev)
+    small = R // 3
+    nbytes = mine._load().sb200_binning_bytes(small)
+    guard = 4096
+    bin_buf = torch.full((nbytes + 2 * guard,), 0x5A, dtype=torch.uint8, device=dev)
+    pl_buf = torch.full((small + 2 * guard,), 0x5A5A5A5A, dtype=torch.int32, device=dev)
+    b.binning, b.point_list, b.pair_capacity = bin_buf[guard:guard + nbytes], pl_buf[guard:guard + small], small
+    b.forward_async(*args)
+    torch.cuda.synchronize()
+    assert (bin_buf[:guard] == 0x5A).all() and (bin_buf[guard + nbytes:] == 0x5A).all()
+    assert (pl_buf[:guard] == 0x5A5A5A5A).all() and (pl_buf[guard + small:] == 0x5A5A5A5A).all()
+    assert not b.confirm() and b.pair_capacity >= R
+    b.forward(*args)
+    torch.cuda.synchronize()
+    for x, y in zip((b.color, b.allmap, b.radii, b.point_list[:R]), ref):
+        assert torch.equal(x, y)

@@ -154,13 +154,12 @@ int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* 
     return 0;
 }
 
-int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* geom_ws, void* binning_ws,
-                         uint32_t* point_list, void* image_ws, float* out_color, float* out_others, void* stream) {
-    g_err[0] = 0;
+static int forward_finish_impl(int P, int W, int H, int64_t R, int R_is_capacity, const float* bg, void* geom_ws,
+                               void* binning_ws, uint32_t* point_list, void* image_ws, float* out_color,
+                               float* out_others, cudaStream_t s) {
     if (check_dims(P, W, H)) return 1;
     if (!bg || !image_ws || !out_color || !out_others) { sb_set_error("forward_finish: NULL input"); return 1; }
     if (R > 0 && (!geom_ws || !binning_ws || !point_list)) { sb_set_error("forward_finish: NULL workspace"); return 1; }
-    cudaStream_t s = (cudaStream_t)stream;
     const int tiles = ((W + SB_TILE_X - 1) / SB_TILE_X) * ((H + SB_TILE_Y - 1) / SB_TILE_Y);
     SbImageLayout IL = sb_image_layout(W, H);
     uint32_t* tile_counts = (uint32_t*)((char*)image_ws + IL.counts);
@@ -169,8 +168,9 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
     const SbSortPlan pl = sb_sort_plan((int)sb_higher_msb((uint32_t)tiles));  // the reference's tile bit count (:410)
     int rc;
     SB_CUDA_CHECK(cudaMemsetAsync(tile_counts, 0, (size_t)tiles * 4, s));
-    if (R > 0) {
+    if (R > 0 && P > 0) {
         SbBinLayout BL = sb_bin_layout(R);
+        SbGeomLayout GL = sb_geom_layout(P);
         char* bw = (char*)binning_ws;
         uint32_t* kbuf[2] = {(uint32_t*)(bw + BL.keys_b), (uint32_t*)(bw + BL.keys_a)};
         uint32_t* vbuf[2] = {(uint32_t*)(bw + BL.vals_b), (uint32_t*)(bw + BL.vals_a)};
@@ -178,8 +178,8 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
                                       (BL.status - BL.zero_begin) + sb_sort_status_bytes(R, pl.passes, 0), s));
         {
             StageScope sc(SB200_STAGE_DUPLICATE, s);
-            rc = sb_launch_duplicate(P, W, H, R, (const char*)geom_ws, (uint32_t*)(bw + BL.chunk_first), tile_counts,
-                                     kbuf[1], vbuf[1], s);
+            rc = sb_launch_duplicate(P, W, H, R, R_is_capacity, (const char*)geom_ws, (uint32_t*)(bw + BL.chunk_first),
+                                     tile_counts, kbuf[1], vbuf[1], s);
         }
         if (rc) return rc;
         {
@@ -189,7 +189,9 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
         if (rc) return rc;
         {
             StageScope sc(SB200_STAGE_SORT, s);
-            rc = sb_launch_sort_passes(pl, 0, kbuf[1], vbuf[1], kbuf, vbuf, point_list, R, nullptr,
+            // little-endian: the low word of the 64-bit pair count (R < 2^30 is checked on the capacity)
+            const uint32_t* n_dev = R_is_capacity ? (const uint32_t*)((const char*)geom_ws + GL.counts) : nullptr;
+            rc = sb_launch_sort_passes(pl, 0, kbuf[1], vbuf[1], kbuf, vbuf, point_list, R, n_dev,
                                        (const uint32_t*)(bw + BL.hist), (uint32_t*)(bw + BL.tickets),
                                        (uint32_t*)(bw + BL.status), s);
         }
@@ -202,6 +204,58 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* 
     // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does
     StageScope sc(SB200_STAGE_BLEND_FWD, s);
     return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others, s);
+}
+
+int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* geom_ws, void* binning_ws,
+                         uint32_t* point_list, void* image_ws, float* out_color, float* out_others, void* stream) {
+    g_err[0] = 0;
+    return forward_finish_impl(P, W, H, R, 0, bg, geom_ws, binning_ws, point_list, image_ws, out_color, out_others,
+                               (cudaStream_t)stream);
+}
+
+int sb200_forward_async(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                        const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
+                        const float* bg, void* geom_ws, int* radii, void* binning_ws, int64_t pair_capacity,
+                        uint32_t* point_list, void* image_ws, float* out_color, float* out_others,
+                        int64_t* num_rendered_host, void* stream) {
+    g_err[0] = 0;
+    if (check_dims(P, W, H)) return 1;
+    if (!num_rendered_host) { sb_set_error("num_rendered_host is NULL"); return 1; }
+    if (pair_capacity < 1) { sb_set_error("forward_async: pair_capacity must be positive"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaEvent_t ev = sync_event();
+    if (!ev) { sb_set_error("forward_async: no event"); return 2; }
+    *num_rendered_host = 0;
+    int rc;
+    if (P > 0) {
+        if (!means3D || !scales || !rotations || !opacities || !colors || !viewmatrix || !projmatrix || !geom_ws || !radii) {
+            sb_set_error("forward_async: NULL input");
+            return 1;
+        }
+        {
+            StageScope sc(SB200_STAGE_PREPROCESS, s);
+            rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
+                                      (char*)geom_ws, radii, s);
+        }
+        if (rc) return rc;
+        SbGeomLayout L = sb_geom_layout(P);
+        SB_CUDA_CHECK(cudaMemcpyAsync(num_rendered_host, (char*)geom_ws + L.counts, 8, cudaMemcpyDeviceToHost, s));
+        SB_CUDA_CHECK(cudaEventRecord(ev, s));
+        StageScope sc(SB200_STAGE_SURFEL_SORT, s);
+        rc = sb_launch_surfel_sort(P, (char*)geom_ws, s);
+        if (rc) return rc;
+    } else {
+        SB_CUDA_CHECK(cudaEventRecord(ev, s));
+    }
+    return forward_finish_impl(P, W, H, P > 0 ? pair_capacity : 0, 1, bg, geom_ws, binning_ws, point_list, image_ws,
+                               out_color, out_others, s);
+}
+
+int sb200_forward_wait(void) {
+    cudaEvent_t ev = sync_event();
+    if (!ev) { sb_set_error("forward_wait: no event"); return 2; }
+    SB_CUDA_CHECK(cudaEventSynchronize(ev));
+    return 0;
 }
 
 int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,

@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(OFF_THREADS)
 sb_pair_offsets_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* __restrict__ n_visible,
                        const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ ticket,
                        unsigned long long* __restrict__ scan_state, uint32_t* __restrict__ offsets,
-                       uint32_t* __restrict__ chunk_first) {
+                       uint32_t* __restrict__ chunk_first, uint32_t max_chunks) {
     __shared__ uint32_t s_warp[OFF_THREADS / 32];
     __shared__ uint32_t s_blk, s_prefix;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
@@ -117,7 +117,8 @@ sb_pair_offsets_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* 
             run += cnt[k];
             offsets[i0 + k] = run;
             // this surfel owns the first pair of every chunk that starts inside [e, run)
-            for (uint32_t c = (e + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK; c * SB_EMIT_CHUNK < run; c++) chunk_first[c] = i0 + k;
+            for (uint32_t c = (e + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK; c * SB_EMIT_CHUNK < run && c < max_chunks; c++)
+                chunk_first[c] = i0 + k;
         }
     }
 }
@@ -127,7 +128,8 @@ sb_pair_offsets_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* 
 
 // dynamic shared memory: uint32 s_hist[hist_words] (tile counts of this CTA; 0 words = count with global REDs)
 __global__ void __launch_bounds__(DUP_THREADS)
-sb_duplicate_kernel(uint32_t grid_x, int64_t R, const uint32_t* __restrict__ sorted_ids,
+sb_duplicate_kernel(uint32_t grid_x, int64_t R, const unsigned long long* __restrict__ R_dev,
+                    const uint32_t* __restrict__ sorted_ids,
                     const uint32_t* __restrict__ n_visible, const ushort4* __restrict__ rects,
                     const uint32_t* __restrict__ offsets, const uint32_t* __restrict__ chunk_first,
                     uint32_t* __restrict__ tile_counts, uint32_t* __restrict__ keys, uint32_t* __restrict__ vals,
@@ -137,6 +139,7 @@ sb_duplicate_kernel(uint32_t grid_x, int64_t R, const uint32_t* __restrict__ sor
     const int tid = threadIdx.x;
     const uint32_t V = __ldg(n_visible);
     for (int t = tid; t < hist_words; t += DUP_THREADS) s_hist[t] = 0;
+    if (R_dev) R = min(R, (int64_t)__ldg(R_dev));  // R is the scratch capacity: emit what fits (caller re-runs)
     const uint32_t nchunks = (uint32_t)((R + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK);
     for (uint32_t c = blockIdx.x; c < nchunks; c += gridDim.x) {
         const uint32_t begin = c * SB_EMIT_CHUNK;
@@ -189,8 +192,9 @@ sb_duplicate_kernel(uint32_t grid_x, int64_t R, const uint32_t* __restrict__ sor
         if (s_hist[t]) atomicAdd(tile_counts + t, s_hist[t]);
 }
 
-int sb_launch_duplicate(int P, int W, int H, int64_t R, const char* geom, uint32_t* chunk_first, uint32_t* tile_counts,
-                        uint32_t* keys, uint32_t* vals, cudaStream_t s) {
+// R_is_capacity: R is the size of the caller's scratch and the live count is read from the geometry workspace
+int sb_launch_duplicate(int P, int W, int H, int64_t R, int R_is_capacity, const char* geom, uint32_t* chunk_first,
+                        uint32_t* tile_counts, uint32_t* keys, uint32_t* vals, cudaStream_t s) {
     if (P == 0 || R <= 0) return 0;
     SbGeomLayout L = sb_geom_layout(P);
     const uint32_t grid_x = (W + SB_TILE_X - 1) / SB_TILE_X;
@@ -202,7 +206,8 @@ int sb_launch_duplicate(int P, int W, int H, int64_t R, const char* geom, uint32
     sb_pair_offsets_kernel<<<oblocks, OFF_THREADS, 0, s>>>(sorted_ids, n_visible, (const uint32_t*)(geom + L.tiles),
                                                            (uint32_t*)(geom + L.tickets) + 4,
                                                            (unsigned long long*)(geom + L.dup_state), offsets,
-                                                           chunk_first);
+                                                           chunk_first,
+                                                           (uint32_t)((R + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK));
     // shared-memory tile histogram when it fits beside the window (up to ~40 k tiles), else global REDs
     static int max_dyn = -1;
     if (max_dyn < 0) {
@@ -214,7 +219,7 @@ int sb_launch_duplicate(int P, int W, int H, int64_t R, const char* geom, uint32
     const int per_sm = hist_words * 4 > 64 * 1024 ? 1 : (hist_words * 4 > 24 * 1024 ? 2 : 4);
     const int grid = (int)(nchunks < 148 * per_sm ? nchunks : 148 * per_sm);
     sb_duplicate_kernel<<<grid, DUP_THREADS, (size_t)hist_words * 4, s>>>(
-        grid_x, R, sorted_ids, n_visible, (const ushort4*)(geom + L.rect), offsets, chunk_first, tile_counts, keys, vals,
+        grid_x, R, R_is_capacity ? (const unsigned long long*)(geom + L.counts) : nullptr, sorted_ids, n_visible, (const ushort4*)(geom + L.rect), offsets, chunk_first, tile_counts, keys, vals,
         hist_words);
     sb_count_launch(2);
     SB_CUDA_CHECK(cudaGetLastError());

@@ -196,8 +196,8 @@ int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float*
                          const float* projmatrix, char* geom, int* radii, cudaStream_t s);
 int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
 int sb_launch_surfel_sort(int P, char* geom, cudaStream_t s);
-int sb_launch_duplicate(int P, int W, int H, int64_t R, const char* geom, uint32_t* chunk_first, uint32_t* tile_counts,
-                        uint32_t* keys, uint32_t* vals, cudaStream_t s);
+int sb_launch_duplicate(int P, int W, int H, int64_t R, int R_is_capacity, const char* geom, uint32_t* chunk_first,
+                        uint32_t* tile_counts, uint32_t* keys, uint32_t* vals, cudaStream_t s);
 int sb_launch_sort_hist(const uint32_t* keys, int64_t n, const SbSortPlan& pl, int drop_invalid, uint32_t* digit_base,
                         uint32_t* n_valid, cudaStream_t s);
 int sb_launch_sort_passes(const SbSortPlan& pl, int small, const uint32_t* keys_in, const uint32_t* vals_in,

@@ -60,6 +60,10 @@ def _load():
     lib.sb200_forward_begin.argtypes = [_i32, _i32, _i32] + [_vp] * 7 + [_vp, _vp, _vp, _vp]
     lib.sb200_forward_finish.restype = _i32
     lib.sb200_forward_finish.argtypes = [_i32, _i32, _i32, _i64] + [_vp] * 8
+    lib.sb200_forward_async.restype = _i32
+    lib.sb200_forward_async.argtypes = [_i32, _i32, _i32] + [_vp] * 8 + [_vp, _vp, _vp, _i64] + [_vp] * 6
+    lib.sb200_forward_wait.restype = _i32
+    lib.sb200_forward_wait.argtypes = []
     lib.sb200_backward.restype = _i32
     lib.sb200_backward.argtypes = [_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 24
     lib.sb200_mark_visible.restype = _i32

@@ -75,6 +75,8 @@ class RasterWorkspace:
         self.loss_ws = u8(lib.sb200_map_loss_bytes(W, H))
         self.binning = u8(0)
         self.point_list = torch.empty(0, dtype=torch.int32, device=device)
+        self.pair_capacity = 0   # pairs the binning scratch and point_list hold
+        self._pending = None     # (pinned count, capacity) of an unconfirmed forward_async
         self.color, self.allmap = f(3, H, W), f(7, H, W)
         self.loss_out = (f(7), f(3, H, W), f(7, H, W))
         self.pixel_mask = torch.ones(H * W, dtype=torch.bool, device=device)
@@ -117,15 +119,65 @@ class RasterWorkspace:
         R = int(count[0])
         self.R = R
         last_counters.update(P=P, R=R, W=W, H=H)
-        need = lib.sb200_binning_bytes(R)
-        if self.binning.numel() < need:
-            self.binning = torch.empty(int(need * 1.25) + 4096, dtype=torch.uint8, device=dev)
-        if self.point_list.numel() < R:
-            self.point_list = torch.empty(int(R * 1.25) + 1024, dtype=torch.int32, device=dev)
+        if R > self.pair_capacity:
+            self._grow_pairs(R)
         _check(lib.sb200_forward_finish(P, W, H, R, _ptr(bg), _ptr(self.geom), _vp(self.binning.data_ptr()),
                                         _vp(self.point_list.data_ptr()), _ptr(self.image), _ptr(self.color),
                                         _ptr(self.allmap), stream), "sb200_forward_finish")
         return self.color, self.radii, self.allmap
+
+    def forward_async(self, means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix):
+        """The same forward without a host synchronisation: the binning scratch kept from earlier views is used as
+        is and the pair count stays on the device.  ``confirm()`` must be called before the view's results are
+        committed; it returns False when the scratch was too small (then it has been grown: run ``forward`` again).
+        The first call (no scratch yet) falls back to the synchronising ``forward``."""
+        lib = _load()
+        P, W, H, dev = self.P, self.W, self.H, self.device
+        cap = min(self.point_list.numel(), self.pair_capacity)
+        if cap < 1:
+            self._pending = None
+            return self.forward(means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix)
+        count = _count_buffer(dev)
+        _check(lib.sb200_forward_async(P, W, H, _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(opacities),
+                                       _ptr(colors), _ptr(viewmatrix), _ptr(projmatrix), _ptr(bg), _ptr(self.geom),
+                                       _ptr(self.radii), _vp(self.binning.data_ptr()), cap,
+                                       _vp(self.point_list.data_ptr()), _ptr(self.image), _ptr(self.color),
+                                       _ptr(self.allmap), _vp(count.data_ptr()), _stream(dev)), "sb200_forward_async")
+        self.R = cap  # what sb200_backward is told; the live count stays on the device
+        self._pending = (count, cap)
+        return self.color, self.radii, self.allmap
+
+    def confirm(self):
+        """Wait for the pair count of the last ``forward_async`` (long since copied when called late in the view) and
+        check it against the scratch capacity."""
+        if self._pending is None:
+            return True
+        count, cap = self._pending
+        self._pending = None
+        _check(_load().sb200_forward_wait(), "sb200_forward_wait")
+        R = int(count[0])
+        last_counters.update(P=self.P, R=R, W=self.W, H=self.H)
+        if R <= cap:
+            return True
+        self._grow_pairs(R)
+        return False
+
+    def _grow_pairs(self, R):
+        lib = _load()
+        need = lib.sb200_binning_bytes(R)
+        if self.binning.numel() < need:
+            self.binning = torch.empty(int(need * 1.25) + 4096, dtype=torch.uint8, device=self.device)
+        if self.point_list.numel() < R:
+            self.point_list = torch.empty(int(R * 1.25) + 1024, dtype=torch.int32, device=self.device)
+        # largest pair count both buffers hold (sb200_binning_bytes is monotone: bisect)
+        lo, hi = 0, self.point_list.numel()
+        while lo < hi:
+            mid = (lo + hi + 1) // 2
+            if lib.sb200_binning_bytes(mid) <= self.binning.numel():
+                lo = mid
+            else:
+                hi = mid - 1
+        self.pair_capacity = lo
 
     def backward(self, d_color, d_allmap, means3D, scales, rotations, bg, viewmatrix, projmatrix, tanfovx, tanfovy,
                  pixel_mask=None):

@@ -308,7 +308,7 @@ class SurfelMapper:
 
     @torch.no_grad()
     def _train_view_fused(self, view, gt, kf_id):
-        """The same iteration in 20 launches of the library: activate -> rasterizer forward -> fused loss ->
+        """The same iteration in 22 launches of the library: activate -> rasterizer forward -> fused loss ->
         rasterizer backward -> one per-surfel update kernel (two around the all-reduce with world_size > 1)."""
         mp, ws = self.mod.mapping, self._ws
         prm = [getattr(self, k).data for k in GROUPS]
@@ -317,12 +317,19 @@ class SurfelMapper:
         lr = [g["lr"] for g in self.optimizer.param_groups]
         eps = self.optimizer.param_groups[0]["eps"]
         opac, scales, rot = mp.activate(prm[2], prm[3], prm[4], out=self._act)
-        ws.forward(prm[0], scales, rot, opac, prm[1], self.bg, view["viewmatrix"], view["projmatrix"])
-        loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gt["rgb"], gt["depth"], gt["depth_cov"], view["w2c"],
-                                              self.cx, self.cy, self.fx, self.fy, self.weights, ws=ws.loss_ws,
-                                              out=ws.loss_out)
-        ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
-                    view["tanfovx"], view["tanfovy"])
+        raster = ws.forward_async
+        while True:
+            raster(prm[0], scales, rot, opac, prm[1], self.bg, view["viewmatrix"], view["projmatrix"])
+            loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gt["rgb"], gt["depth"], gt["depth_cov"],
+                                                  view["w2c"], self.cx, self.cy, self.fx, self.fy, self.weights,
+                                                  ws=ws.loss_ws, out=ws.loss_out)
+            ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
+                        view["tanfovx"], view["tanfovy"])
+            # the only host wait of the view: the pair count, copied back right after the preprocess, with the whole
+            # view already queued.  False = the binning scratch was too small (it has been grown): run again.
+            if ws.confirm():
+                break
+            raster = ws.forward
         book = (self._stable_mask, self._local_scores, self._global_scores, self._globalkf_max_scores, self._globalkf_id)
         if self.world_size > 1:
             mp.surfel_update(mp.UPDATE_DP_PRE, prm, m, v, lr, ws, *book, kf_id, fused=self._fused, eps=eps)
