@@ -187,9 +187,9 @@ def test_api_errors(mine):
              scales=inp["scales"], rotations=inp["rotations"])
 
 
-@pytest.mark.parametrize("name", ["C2", "C3"])
+@pytest.mark.parametrize("name", ["C2", "C3", "C4"])
 def test_full_size_properties(mine, name):
-    """BASELINE.json sizes (1.2 M / 500 k surfels): properties that need no oracle."""
+    """BASELINE.json sizes (1.2 M / 500 k / 5 M surfels at 1080p): properties that need no oracle."""
     scene, views = synthetic.make_scene(name)
     inp = util.cuda_inputs(synthetic.view_inputs(scene, views[-1]))
     W, H = inp["W"], inp["H"]
