@@ -100,12 +100,12 @@ __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
             g[3 + k] = a.d_colors[3 * iz + k];
         }
         g[6] = a.d_opacity[i];
-        g[7] = a.d_scales[2 * iz];
-        g[8] = a.d_scales[2 * iz + 1];
+        const float2 ds = ((const float2*)a.d_scales)[i];
+        g[7] = ds.x; g[8] = ds.y;
         const float4 dq = ((const float4*)a.d_rot)[i];
         g[9] = dq.x; g[10] = dq.y; g[11] = dq.z; g[12] = dq.w;
-        cur0 = a.cur_scores[2 * iz];
-        cur1 = a.cur_scores[2 * iz + 1];
+        const float2 cs = ((const float2*)a.cur_scores)[i];
+        cur0 = cs.x; cur1 = cs.y;
     }
     float glob0 = a.global_scores[2 * iz], glob1 = 0.f, loc0 = 0.f, loc1 = 0.f, kfm = 0.f;
     if (mode != SB200_UPDATE_DP_PRE) {
@@ -117,12 +117,28 @@ __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
     // raw opacity / scaling / rotation feed the activation backward of every surfel; the rest is Adam state
     const bool need_raw = mode != SB200_UPDATE_DP_POST;
 #pragma unroll
-    for (int c = 0; c < 13; c++) {
+    for (int c = 0; c < 7; c++) {  // xyz, rgb ([P,3] rows: scalar accesses), opacity
         const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
         const size_t e = iz * nc + (c - SB_GRP_C0(grp));
         pv[c] = (adam || (need_raw && c >= 6)) ? a.param[grp][e] : 0.f;
         mv[c] = adam ? a.m[grp][e] : 0.f;
         vv[c] = adam ? a.v[grp][e] : 0.f;
+    }
+    {   // scaling [P,2] and rotation [P,4] rows as one 64- / 128-bit access each (tensor bases are 16-B aligned)
+        float2 s2 = make_float2(0.f, 0.f), ms2 = s2, vs2 = s2;
+        float4 q4 = make_float4(0.f, 0.f, 0.f, 0.f), mq4 = q4, vq4 = q4;
+        if (adam || need_raw) {
+            s2 = ((const float2*)a.param[3])[i];
+            q4 = ((const float4*)a.param[4])[i];
+        }
+        if (adam) {
+            ms2 = ((const float2*)a.m[3])[i]; vs2 = ((const float2*)a.v[3])[i];
+            mq4 = ((const float4*)a.m[4])[i]; vq4 = ((const float4*)a.v[4])[i];
+        }
+        pv[7] = s2.x; pv[8] = s2.y; mv[7] = ms2.x; mv[8] = ms2.y; vv[7] = vs2.x; vv[8] = vs2.y;
+        pv[9] = q4.x; pv[10] = q4.y; pv[11] = q4.z; pv[12] = q4.w;
+        mv[9] = mq4.x; mv[10] = mq4.y; mv[11] = mq4.z; mv[12] = mq4.w;
+        vv[9] = vq4.x; vv[10] = vq4.y; vv[11] = vq4.z; vv[12] = vq4.w;
     }
 
     if (mode != SB200_UPDATE_DP_POST) {
@@ -178,16 +194,28 @@ __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
 
     // ---- masked Adam without bias correction (adam.cu:9-38) ----
     if (adam) {
+        float pn[13], mn[13], vn[13];
 #pragma unroll
         for (int c = 0; c < 13; c++) {
+            const int grp = SB_GRP(c);
+            mn[c] = a.b1 * mv[c] + (1.0f - a.b1) * g[c];
+            vn[c] = a.b2 * vv[c] + (1.0f - a.b2) * g[c] * g[c];
+            pn[c] = pv[c] + -a.lr[grp] * mn[c] / (sqrtf(vn[c]) + a.eps);
+        }
+#pragma unroll
+        for (int c = 0; c < 7; c++) {
             const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
             const size_t e = iz * nc + (c - SB_GRP_C0(grp));
-            const float m1 = a.b1 * mv[c] + (1.0f - a.b1) * g[c];
-            const float v1 = a.b2 * vv[c] + (1.0f - a.b2) * g[c] * g[c];
-            a.param[grp][e] = pv[c] + -a.lr[grp] * m1 / (sqrtf(v1) + a.eps);
-            a.m[grp][e] = m1;
-            a.v[grp][e] = v1;
+            a.param[grp][e] = pn[c];
+            a.m[grp][e] = mn[c];
+            a.v[grp][e] = vn[c];
         }
+        ((float2*)a.param[3])[i] = make_float2(pn[7], pn[8]);
+        ((float2*)a.m[3])[i] = make_float2(mn[7], mn[8]);
+        ((float2*)a.v[3])[i] = make_float2(vn[7], vn[8]);
+        ((float4*)a.param[4])[i] = make_float4(pn[9], pn[10], pn[11], pn[12]);
+        ((float4*)a.m[4])[i] = make_float4(mn[9], mn[10], mn[11], mn[12]);
+        ((float4*)a.v[4])[i] = make_float4(vn[9], vn[10], vn[11], vn[12]);
     }
 }
 
@@ -216,6 +244,13 @@ extern "C" int sb200_surfel_update(int P, int mode, float* const* params, float*
     }
     if (mode != SB200_UPDATE_DP_PRE && (!stable_mask || !local_scores || !kf_max_scores || !kf_id)) {
         sb_set_error("surfel_update: NULL bookkeeping input");
+        return 1;
+    }
+    // [P,2] and [P,4] rows are accessed as float2 / float4
+    if ((((uintptr_t)params[3] | (uintptr_t)exp_avg[3] | (uintptr_t)exp_avg_sq[3] | (uintptr_t)d_scales |
+          (uintptr_t)cur_scores) & 7) ||
+        (((uintptr_t)params[4] | (uintptr_t)exp_avg[4] | (uintptr_t)exp_avg_sq[4] | (uintptr_t)d_rotations) & 15)) {
+        sb_set_error("surfel_update: scaling / score arrays must be 8-byte, rotation arrays 16-byte aligned");
         return 1;
     }
     SbUpdateArgs a;
