@@ -209,10 +209,12 @@ int sb_launch_duplicate(int P, int W, int H, int64_t R, int R_is_capacity, const
                                                            chunk_first,
                                                            (uint32_t)((R + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK));
     // shared-memory tile histogram when it fits beside the window (up to ~40 k tiles), else global REDs
-    static int max_dyn = -1;
-    if (max_dyn < 0) {
-        max_dyn = 160 * 1024;
+    const int max_dyn = 160 * 1024;
+    static bool attr_set[SB_MAX_DEVICES] = {};  // function attributes are per device
+    const int dev = sb_current_device();
+    if (!attr_set[dev]) {
         SB_CUDA_CHECK(cudaFuncSetAttribute(sb_duplicate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_dyn));
+        attr_set[dev] = true;
     }
     const int hist_words = (size_t)tiles * 4 <= (size_t)max_dyn ? tiles : 0;
     const int64_t nchunks = (R + SB_EMIT_CHUNK - 1) / SB_EMIT_CHUNK;

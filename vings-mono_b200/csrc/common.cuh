@@ -173,6 +173,13 @@ static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
     return msb;
 }
 
+#define SB_MAX_DEVICES 64
+static inline int sb_current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= SB_MAX_DEVICES) dev = 0;
+    return dev;
+}
+
 void sb_set_error(const char* fmt, ...);
 void sb_count_launch(int n);  // kernels launched (reported as gpu_launches by bench.py)
 // Optional per-stage device timing (api.cu): brackets a stage with CUDA events on its launching stream.

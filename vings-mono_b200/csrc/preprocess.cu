@@ -24,7 +24,10 @@ __device__ __forceinline__ void sb_stage_f3(float* dst, const float* __restrict_
     }
 }
 
-__global__ void __launch_bounds__(PRE_THREADS)
+#ifndef PRE_MIN_CTAS
+#define PRE_MIN_CTAS 6
+#endif
+__global__ void __launch_bounds__(PRE_THREADS, PRE_MIN_CTAS)
 sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, const float2* __restrict__ scales,
                      const float4* __restrict__ rotations, const float* __restrict__ opacities,
                      const float* __restrict__ colors, const float* __restrict__ viewmatrix,

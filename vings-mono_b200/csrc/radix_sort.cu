@@ -235,11 +235,12 @@ template <int ITEMS>
 static int sb_run_passes(const SbSortPlan& pl, const uint32_t* keys_in, const uint32_t* vals_in, uint32_t* const kbuf[2],
                          uint32_t* const vbuf[2], uint32_t* vals_final, int64_t n, const uint32_t* n_dev,
                          const uint32_t* digit_base, uint32_t* tickets, uint32_t* status, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static bool attr_set[SB_MAX_DEVICES] = {};  // function attributes are per device
+    const int dev = sb_current_device();
+    if (!attr_set[dev]) {
         SB_CUDA_CHECK(cudaFuncSetAttribute(sb_onesweep_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            (int)sizeof(SortSmem<ITEMS>)));
-        attr_set = true;
+        attr_set[dev] = true;
     }
     const int64_t ntiles = (n + SB_SORT_THREADS * ITEMS - 1) / (SB_SORT_THREADS * ITEMS);
     const uint32_t* kin = keys_in;
