@@ -225,14 +225,33 @@ def main():
             v = (s * VIEWS_PER_STEP + i + rank) % K
             mapper.train_view(view_dev[v], gt_dev[v], kf_id=v)
 
-    def step_e2e(s):
-        for i in range(VIEWS_PER_STEP):
-            v = (s * VIEWS_PER_STEP + i + rank) % K
+    copy_stream = torch.cuda.Stream(device=dev)
+
+    def stage(v):
+        """Queue the host->device copies of one view's inputs on the copy stream (pinned source, so they run while
+        the previous view computes); returns the device tensors and the event the compute stream waits for."""
+        with torch.cuda.stream(copy_stream):
             gt = {k: t.to(dev, non_blocking=True) for k, t in gt_host[v].items()}
             vw = {k: (t.to(dev, non_blocking=True) if isinstance(t, torch.Tensor) else t) for k, t in view_host[v].items()}
-            loss = mapper.train_view(vw, gt, kf_id=v)
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+        return gt, vw, ev
+
+    def step_e2e(s):
+        cur = torch.cuda.current_stream()
+        ids = [(s * VIEWS_PER_STEP + i + rank) % K for i in range(VIEWS_PER_STEP)]
+        copy_stream.wait_stream(cur)       # every copy of the step starts inside the step
+        nxt = stage(ids[0])
+        for i in range(VIEWS_PER_STEP):
+            gt, vw, ev = nxt
+            if i + 1 < VIEWS_PER_STEP:
+                nxt = stage(ids[i + 1])    # prefetch the next view of this step behind the current one
+            cur.wait_event(ev)
+            for t in list(gt.values()) + [t for t in vw.values() if isinstance(t, torch.Tensor)]:
+                t.record_stream(cur)
+            loss = mapper.train_view(vw, gt, kf_id=ids[i])
             loss_host[i:i + 1].copy_(loss.reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()  # the step's result is on the host
+        cur.synchronize()  # the step's result is on the host
 
     def barrier():
         if world > 1:
@@ -260,11 +279,15 @@ def main():
 
     clocks = ClockSampler(local_rank) if rank == 0 else None
     mine = args.impl == "b200"
-    if mine:
-        mod.profile_enable(True)
-        mod.profile_read()
     l0 = mod.launch_count() if mine else 0
+    ms_val, t0, t1 = timed(step_resident, args.steps, args.warmup)
+    launches = (mod.launch_count() - l0) if mine else 0
+    # warm-up launches are in the counter too; scale launches to the timed steps only
+    launches = launches * args.steps // (args.steps + args.warmup)
+    # per-stage device times (roofline): the same K steps once more with the library's stage events switched on
+    # (two event records per stage cost ~1.5 % of a view, so they stay out of the pass `value` is taken from)
     R_seen = []
+    stage_ms = {}
     if mine:
         orig_train = mapper.train_view
 
@@ -273,14 +296,13 @@ def main():
             R_seen.append(mod.last_counters.get("R", 0))
             return out
         mapper.train_view = train_and_count
-    ms_val, t0, t1 = timed(step_resident, args.steps, args.warmup)
-    launches = (mod.launch_count() - l0) if mine else 0
-    stage_ms = mod.profile_read() if mine else {}
-    if mine:
+        mod.profile_enable(True)
+        mod.profile_read()
+        timed(step_resident, args.steps, 0)
+        stage_ms = mod.profile_read()
         mod.profile_enable(False)
-        # warm-up launches are in the counters too; scale launches to the timed steps only
-        launches = launches * args.steps // (args.steps + args.warmup)
-    R_timed = R_seen[args.warmup * VIEWS_PER_STEP:] if mine else []
+        mapper.train_view = orig_train
+    R_timed = R_seen
     ms_e2e, _, t2 = timed(step_e2e, args.steps, max(1, args.warmup // 2))
     clk = clocks.summary(t0, t2) if clocks else None
     if clocks:
@@ -308,6 +330,9 @@ def main():
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches, "clocks": clk,
     }
+    out["config"]["e2e_inputs"] = ("pinned host -> device copies of every view's ground truth and camera on a copy stream, "
+                                   "the next view of the step prefetched behind the current one; loss read back per view")
+    out["config"]["stage_timing"] = "per-stage CUDA events from an instrumented repeat of the same steps, not from the pass `value` times"
     if args.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": "views/s", "cores": os.cpu_count(), "kind": "reference",
@@ -377,7 +402,7 @@ def main():
         stages = {}
         for name, (ms, cnt) in stage_ms.items():
             if cnt:
-                # the counters include the warm-up steps; every launch of a stage is timed the same way
+                # from the instrumented repeat of the timed steps (see above)
                 per = ms / cnt
                 stages[name] = {"ms_per_launch": per, "launches": cnt,
                                 "GBps": stage_bytes(name, counters) / (per * 1e-3) / 1e9}
