@@ -54,6 +54,7 @@ CASES = [
     ("C1", dict(P=3000, W=200, H=150)),                    # ragged image (not a multiple of the 16-px tile)
     ("C3", dict(P=60000, bg=(0.3, 0.1, 0.7))),             # indoor, non-zero background (quirk Q6)
     ("C2", dict(P=150000)),                                # KITTI-shaped wide image
+    ("C1", dict(P=4000, W=4112, H=2600)),                  # 41 891 tiles: 16 tile bits, tile counts by global REDs
 ]
 
 
