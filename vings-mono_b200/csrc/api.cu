@@ -12,6 +12,9 @@
 #include <vector>
 
 static thread_local char g_err[512] = "";
+#ifndef SB_PAIR_SMALL
+#define SB_PAIR_SMALL 0  // pair sort on 4096-pair tiles (1 = 2048)
+#endif
 
 // ---- optional per-stage device timing (CUDA events on the launching stream) and launch counting ----
 static std::atomic<long long> g_launches{0};
@@ -175,7 +178,7 @@ static int forward_finish_impl(int P, int W, int H, int64_t R, int R_is_capacity
         uint32_t* kbuf[2] = {(uint32_t*)(bw + BL.keys_b), (uint32_t*)(bw + BL.keys_a)};
         uint32_t* vbuf[2] = {(uint32_t*)(bw + BL.vals_b), (uint32_t*)(bw + BL.vals_a)};
         SB_CUDA_CHECK(cudaMemsetAsync(bw + BL.zero_begin, 0,
-                                      (BL.status - BL.zero_begin) + sb_sort_status_bytes(R, pl.passes, 0), s));
+                                      (BL.status - BL.zero_begin) + sb_sort_status_bytes(R, pl.passes, SB_PAIR_SMALL), s));
         {
             StageScope sc(SB200_STAGE_DUPLICATE, s);
             rc = sb_launch_duplicate(P, W, H, R, R_is_capacity, (const char*)geom_ws, (uint32_t*)(bw + BL.chunk_first),
@@ -191,7 +194,7 @@ static int forward_finish_impl(int P, int W, int H, int64_t R, int R_is_capacity
             StageScope sc(SB200_STAGE_SORT, s);
             // little-endian: the low word of the 64-bit pair count (R < 2^30 is checked on the capacity)
             const uint32_t* n_dev = R_is_capacity ? (const uint32_t*)((const char*)geom_ws + GL.counts) : nullptr;
-            rc = sb_launch_sort_passes(pl, 0, kbuf[1], vbuf[1], kbuf, vbuf, point_list, R, n_dev,
+            rc = sb_launch_sort_passes(pl, SB_PAIR_SMALL, kbuf[1], vbuf[1], kbuf, vbuf, point_list, R, n_dev,
                                        (const uint32_t*)(bw + BL.hist), (uint32_t*)(bw + BL.tickets),
                                        (uint32_t*)(bw + BL.status), s);
         }

@@ -160,6 +160,10 @@ sb_onesweep_kernel(const uint32_t* __restrict__ keys_in, const uint32_t* __restr
             // the walk is a serial chain of L2 latencies, one hop per load otherwise
             int64_t t = (int64_t)tile - 1;
             bool done = false;
+            {   // steady state: the predecessor already holds its inclusive prefix
+                const uint32_t w0 = st[(size_t)t * SB_RADIX + d];
+                if (w0 & ST_FLAG_INC) { prefix = w0 & ST_VAL_MASK; done = true; }
+            }
             while (!done) {
                 uint32_t w[SB_LOOKBACK];
 #pragma unroll
