@@ -208,6 +208,37 @@ size_t sb200_prune_scratch_bytes(int64_t P);
 int sb200_prune_rows(int P, const uint8_t* delete_mask, int n_arrays, const void* const* src, void* const* dst,
                      const int* row_bytes, void* scratch, int* kept_host, void* stream);
 
+/* ---- precomputed splat transforms (the rasterizer's `cov3D_precomp` = transMat_precomp input; unused by VINGS-Mono) ----
+ * transMat_precomp [P,9]: rows Tu, Tv, Tw of every surfel's splat-to-pixel transform, used instead of scales +
+ * rotations (cuda_rasterizer/forward.cu:204-219: the normal becomes (0,0,1)).  Stage 2 is sb200_forward_finish.
+ * The backward (backward.cu:875-883,950-964) then produces dL_dtransMat [P,9] (required), dL_dcolors, dL_dopacity,
+ * scores and the dL_dmeans2D heuristic; dL_dmeans3D / dL_dscales / dL_drotations are written as zero rows. */
+int sb200_forward_begin_precomp(int P, int W, int H, const float* means3D, const float* transMat_precomp,
+                                const float* opacities, const float* colors, const float* viewmatrix,
+                                const float* projmatrix, void* geom_ws, int* radii, int64_t* num_rendered_host,
+                                void* stream);
+int sb200_backward_precomp(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                           const float* transMat_precomp, const float* viewmatrix, const float* projmatrix,
+                           const int* radii, const void* geom_ws, const uint32_t* point_list, const void* image_ws,
+                           const float* out_color, const float* out_others, const float* dL_dout_color,
+                           const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws, float* dL_dmeans3D,
+                           float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dscales,
+                           float* dL_drotations, float* dL_dtransMat, float* scores, void* stream);
+
+/* ---- spherical-harmonics colours (the rasterizer's `shs` / `sh_degree` inputs; unused by VINGS-Mono) ----------
+ * The reference evaluates SH inside its preprocess kernels (computeColorFromSH, cuda_rasterizer/forward.cu:28-79,
+ * backward.cu:20-139); here it is a stage in front of / behind the rasterizer:
+ *   sb200_sh_forward : colors[P,3] = max(0, sum_k basis_k(dir) * shs[:,k,:] + 0.5), dir = normalize(means3D - campos),
+ *                      degree 0..3, shs [P, n_coeffs, 3] with n_coeffs >= (degree+1)^2; clamped[P,3] (u8) = was < 0.
+ *                      Pass `colors` to sb200_forward_begin as the colours.
+ *   sb200_sh_backward: from sb200_backward's dL_dcolors: dL_dsh [P, n_coeffs, 3] (fully written; zero rows for
+ *                      radii <= 0, zero above the active degree) and dL_dmeans3D += the view-direction term. */
+int sb200_sh_forward(int P, int degree, int n_coeffs, const float* means3D, const float* campos /* [3] */,
+                     const float* shs, float* colors, uint8_t* clamped, void* stream);
+int sb200_sh_backward(int P, int degree, int n_coeffs, const float* means3D, const float* campos, const float* shs,
+                      const uint8_t* clamped, const int* radii, const float* dL_dcolors, float* dL_dmeans3D,
+                      float* dL_dsh, void* stream);
+
 /* ---- building blocks exposed for parity tests ----------------------------------------------- */
 /* Stable LSD radix sort of n (u32 key, u32 value) pairs on key bits [0,end_bit), the sort both binning sorts
  * run on.  scratch = sb200_binning_bytes(n) bytes whose tile ids A / surfel ids A arrays (see layout) hold the

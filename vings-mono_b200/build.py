@@ -16,7 +16,7 @@ VARIANT = os.environ.get("SB200_VARIANT", "")
 OBJ = OBJ + ("_" + VARIANT if VARIANT else "")
 OUT = os.path.join(HERE, "diff_surfel_rasterization", "libsurfel_b200%s.so" % ("_" + VARIANT if VARIANT else ""))
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "radix_sort.cu", "blend_forward.cu", "blend_backward.cu",
-           "preprocess_backward.cu", "map_loss.cu", "surfel_update.cu", "churn.cu"]
+           "preprocess_backward.cu", "map_loss.cu", "surfel_update.cu", "churn.cu", "sh_color.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + os.environ.get("SB200_EXTRA_FLAGS", "").split()
 

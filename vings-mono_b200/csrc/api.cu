@@ -58,7 +58,7 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 5; }
+int sb200_abi_version(void) { return 6; }
 
 long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -123,15 +123,17 @@ static int check_dims(int P, int W, int H) {
     return 0;
 }
 
-int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
-                        const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
-                        void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream) {
+static int forward_begin_impl(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                              const float* transmat, const float* opacities, const float* colors,
+                              const float* viewmatrix, const float* projmatrix, void* geom_ws, int* radii,
+                              int64_t* num_rendered_host, void* stream) {
     g_err[0] = 0;
     if (check_dims(P, W, H)) return 1;
     if (!num_rendered_host) { sb_set_error("num_rendered_host is NULL"); return 1; }
     *num_rendered_host = 0;
     if (P == 0) return 0;  // reference: rasterize_points.cu:106
-    if (!means3D || !scales || !rotations || !opacities || !colors || !viewmatrix || !projmatrix || !geom_ws || !radii) {
+    if (!means3D || (!transmat && (!scales || !rotations)) || !opacities || !colors || !viewmatrix || !projmatrix ||
+        !geom_ws || !radii) {
         sb_set_error("forward_begin: NULL input");
         return 1;
     }
@@ -139,8 +141,8 @@ int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* 
     int rc;
     {
         StageScope sc(SB200_STAGE_PREPROCESS, s);
-        rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
-                                  (char*)geom_ws, radii, s);
+        rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, transmat, opacities, colors, viewmatrix,
+                                  projmatrix, (char*)geom_ws, radii, s);
     }
     if (rc) return rc;
     SbGeomLayout L = sb_geom_layout(P);
@@ -155,6 +157,22 @@ int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* 
     if (ev) SB_CUDA_CHECK(cudaEventSynchronize(ev));
     else SB_CUDA_CHECK(cudaStreamSynchronize(s));
     return 0;
+}
+
+int sb200_forward_begin(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
+                        const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
+                        void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream) {
+    return forward_begin_impl(P, W, H, means3D, scales, rotations, nullptr, opacities, colors, viewmatrix, projmatrix,
+                              geom_ws, radii, num_rendered_host, stream);
+}
+
+int sb200_forward_begin_precomp(int P, int W, int H, const float* means3D, const float* transMat_precomp,
+                                const float* opacities, const float* colors, const float* viewmatrix,
+                                const float* projmatrix, void* geom_ws, int* radii, int64_t* num_rendered_host,
+                                void* stream) {
+    // (a NULL transMat_precomp fails forward_begin_impl's input check: neither a transform nor scales + rotations)
+    return forward_begin_impl(P, W, H, means3D, nullptr, nullptr, transMat_precomp, opacities, colors, viewmatrix,
+                              projmatrix, geom_ws, radii, num_rendered_host, stream);
 }
 
 static int forward_finish_impl(int P, int W, int H, int64_t R, int R_is_capacity, const float* bg, void* geom_ws,
@@ -237,8 +255,8 @@ int sb200_forward_async(int P, int W, int H, const float* means3D, const float* 
         }
         {
             StageScope sc(SB200_STAGE_PREPROCESS, s);
-            rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, opacities, colors, viewmatrix, projmatrix,
-                                      (char*)geom_ws, radii, s);
+            rc = sb_launch_preprocess(P, W, H, means3D, scales, rotations, nullptr, opacities, colors, viewmatrix,
+                                      projmatrix, (char*)geom_ws, radii, s);
         }
         if (rc) return rc;
         SbGeomLayout L = sb_geom_layout(P);
@@ -261,8 +279,9 @@ int sb200_forward_wait(void) {
     return 0;
 }
 
-int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
-                   const float* means3D, const float* scales, const float* rotations, const float* viewmatrix,
+static int backward_impl(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                   const float* means3D, const float* scales, const float* rotations, const float* transmat,
+                   const float* viewmatrix,
                    const float* projmatrix, const int* radii, const void* geom_ws, const uint32_t* point_list,
                    const void* image_ws, const float* out_color, const float* out_others,
                    const float* dL_dout_color, const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws,
@@ -271,7 +290,8 @@ int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfov
     g_err[0] = 0;
     if (check_dims(P, W, H)) return 1;
     if (P == 0) return 0;  // reference: rasterize_points.cu:217
-    if (!geom_ws || !image_ws || !grad_ws || !radii || !dL_dout_color || !dL_dout_others || !pixel_mask ||
+    if ((transmat ? !dL_dtransMat : (!means3D || !scales || !rotations)) ||
+        !geom_ws || !image_ws || !grad_ws || !radii || !dL_dout_color || !dL_dout_others || !pixel_mask ||
         !dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations || !scores) {
         sb_set_error("backward: NULL input");
         return 1;
@@ -289,9 +309,35 @@ int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfov
         SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
     }
     StageScope sc(SB200_STAGE_PREPROCESS_BWD, s);
-    return sb_launch_preprocess_backward(P, W, H, tanfovx, tanfovy, means3D, scales, rotations, viewmatrix, projmatrix,
+    return sb_launch_preprocess_backward(P, W, H, tanfovx, tanfovy, means3D, scales, rotations, transmat, viewmatrix, projmatrix,
                                          radii, (const char*)geom_ws, (const float*)grad_ws, dL_dmeans3D, dL_dmeans2D,
                                          dL_dcolors, dL_dopacity, dL_dscales, dL_drotations, dL_dtransMat, scores, s);
+}
+
+int sb200_backward(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                   const float* means3D, const float* scales, const float* rotations, const float* viewmatrix,
+                   const float* projmatrix, const int* radii, const void* geom_ws, const uint32_t* point_list,
+                   const void* image_ws, const float* out_color, const float* out_others,
+                   const float* dL_dout_color, const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws,
+                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dscales,
+                   float* dL_drotations, float* dL_dtransMat, float* scores, void* stream) {
+    return backward_impl(P, W, H, R, bg, tanfovx, tanfovy, means3D, scales, rotations, nullptr, viewmatrix, projmatrix,
+                         radii, geom_ws, point_list, image_ws, out_color, out_others, dL_dout_color, dL_dout_others,
+                         pixel_mask, grad_ws, dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dscales,
+                         dL_drotations, dL_dtransMat, scores, stream);
+}
+
+int sb200_backward_precomp(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                           const float* transMat_precomp, const float* viewmatrix, const float* projmatrix,
+                           const int* radii, const void* geom_ws, const uint32_t* point_list, const void* image_ws,
+                           const float* out_color, const float* out_others, const float* dL_dout_color,
+                           const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws, float* dL_dmeans3D,
+                           float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dscales,
+                           float* dL_drotations, float* dL_dtransMat, float* scores, void* stream) {
+    return backward_impl(P, W, H, R, bg, tanfovx, tanfovy, nullptr, nullptr, nullptr, transMat_precomp, viewmatrix,
+                         projmatrix, radii, geom_ws, point_list, image_ws, out_color, out_others, dL_dout_color,
+                         dL_dout_others, pixel_mask, grad_ws, dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                         dL_dscales, dL_drotations, dL_dtransMat, scores, stream);
 }
 
 int sb200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -199,8 +199,8 @@ struct SbStageScope {
 
 // Stage launchers (defined in the .cu files, sequenced by api.cu).
 int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
-                         const float* opacities, const float* colors, const float* viewmatrix,
-                         const float* projmatrix, char* geom, int* radii, cudaStream_t s);
+                         const float* transmat_precomp, const float* opacities, const float* colors,
+                         const float* viewmatrix, const float* projmatrix, char* geom, int* radii, cudaStream_t s);
 int sb_launch_mark_visible(int P, const float* means3D, const float* viewmatrix, bool* present, cudaStream_t s);
 int sb_launch_surfel_sort(int P, char* geom, cudaStream_t s);
 int sb_launch_duplicate(int P, int W, int H, int64_t R, int R_is_capacity, const char* geom, uint32_t* chunk_first,
@@ -220,7 +220,8 @@ int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, co
                              const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
                              float* grad_acc, cudaStream_t s);
 int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanfovy, const float* means3D,
-                                  const float* scales, const float* rotations, const float* viewmatrix,
+                                  const float* scales, const float* rotations, const float* transmat_precomp,
+                                  const float* viewmatrix,
                                   const float* projmatrix, const int* radii, const char* geom, const float* grad_acc,
                                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
                                   float* dL_dscales, float* dL_drotations, float* dL_dtransMat, float* scores,

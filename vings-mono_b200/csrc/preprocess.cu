@@ -27,9 +27,13 @@ __device__ __forceinline__ void sb_stage_f3(float* dst, const float* __restrict_
 #ifndef PRE_MIN_CTAS
 #define PRE_MIN_CTAS 6
 #endif
+// PRECOMP: the caller supplies the 3x3 splat-to-pixel transform of every surfel (`transMat_precomp` of the
+// reference, forward.cu:204-219) in place of scales + rotations; the normal is then (0,0,1).
+template <bool PRECOMP>
 __global__ void __launch_bounds__(PRE_THREADS, PRE_MIN_CTAS)
 sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, const float2* __restrict__ scales,
-                     const float4* __restrict__ rotations, const float* __restrict__ opacities,
+                     const float4* __restrict__ rotations, const float* __restrict__ transmat_precomp,
+                     const float* __restrict__ opacities,
                      const float* __restrict__ colors, const float* __restrict__ viewmatrix,
                      const float* __restrict__ projmatrix, float4* __restrict__ rec, float* __restrict__ depths,
                      ushort4* __restrict__ rects, uint32_t* __restrict__ tiles_touched,
@@ -62,10 +66,16 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
         if (!(pz <= 0.2f)) {
             float Tm[9];
             float3 normal;
-            const float4 rot = __ldg(rotations + idx);
-            const float2 scl = __ldg(scales + idx);
-            sb_transmat_pinned(rot.x, rot.y, rot.z, rot.w, scl.x, scl.y, p_orig.x, p_orig.y, p_orig.z, s_pm, s_vm, W, H,
-                               Tm, normal);
+            if (PRECOMP) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) Tm[k] = __ldg(transmat_precomp + 9 * (size_t)idx + k);
+                normal = make_float3(0.0f, 0.0f, 1.0f);
+            } else {
+                const float4 rot = __ldg(rotations + idx);
+                const float2 scl = __ldg(scales + idx);
+                sb_transmat_pinned(rot.x, rot.y, rot.z, rot.w, scl.x, scl.y, p_orig.x, p_orig.y, p_orig.z, s_pm, s_vm,
+                                   W, H, Tm, normal);
+            }
             float2 point_image;
             float radius;
             if (sb_aabb_pinned(Tm, point_image, radius)) {
@@ -125,16 +135,17 @@ __global__ void sb_mark_visible_kernel(int P, const float* __restrict__ means3D,
 }
 
 int sb_launch_preprocess(int P, int W, int H, const float* means3D, const float* scales, const float* rotations,
-                         const float* opacities, const float* colors, const float* viewmatrix,
-                         const float* projmatrix, char* geom, int* radii, cudaStream_t s) {
+                         const float* transmat_precomp, const float* opacities, const float* colors,
+                         const float* viewmatrix, const float* projmatrix, char* geom, int* radii, cudaStream_t s) {
     SbGeomLayout L = sb_geom_layout(P);
     int nblocks = (P + PRE_THREADS - 1) / PRE_THREADS;
     SB_CUDA_CHECK(cudaMemsetAsync(geom + L.state, 0, L.state_bytes, s));
     if (P == 0) return 0;
-    sb_preprocess_kernel<<<nblocks, PRE_THREADS, 0, s>>>(
-        P, W, H, means3D, (const float2*)scales, (const float4*)rotations, opacities, colors, viewmatrix, projmatrix,
-        (float4*)(geom + L.rec), (float*)(geom + L.depth), (ushort4*)(geom + L.rect), (uint32_t*)(geom + L.tiles),
-        (uint32_t*)(geom + L.sort_k[1]), (unsigned long long*)(geom + L.counts), radii);
+    auto kern = transmat_precomp ? sb_preprocess_kernel<true> : sb_preprocess_kernel<false>;
+    kern<<<nblocks, PRE_THREADS, 0, s>>>(
+        P, W, H, means3D, (const float2*)scales, (const float4*)rotations, transmat_precomp, opacities, colors,
+        viewmatrix, projmatrix, (float4*)(geom + L.rec), (float*)(geom + L.depth), (ushort4*)(geom + L.rect),
+        (uint32_t*)(geom + L.tiles), (uint32_t*)(geom + L.sort_k[1]), (unsigned long long*)(geom + L.counts), radii);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

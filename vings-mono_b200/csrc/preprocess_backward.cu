@@ -26,9 +26,14 @@ __device__ __forceinline__ float4 sb_quat_to_rotmat_vjp(float4 quat, const SbMat
     return v;
 }
 
+// PRECOMP (transMat_precomp, backward.cu:875-883,950-964): T is the caller's; only dL/dtransMat (with the centre terms
+// folded in when the low-pass gradient is non-zero), colours, opacity, scores and the densification heuristic
+// are produced -- means3D / scales / rotations get zero rows.
+template <bool PRECOMP>
 __global__ void __launch_bounds__(256)
 sb_preprocess_backward_kernel(int P, int Wq, int Hq, const float* __restrict__ means3D,
                               const float2* __restrict__ scales, const float4* __restrict__ rotations,
+                              const float* __restrict__ transmat_precomp,
                               const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
                               const int* __restrict__ radii, const float4* __restrict__ rec,
                               const float* __restrict__ grad_acc, float* __restrict__ dL_dmeans3D,
@@ -58,19 +63,31 @@ sb_preprocess_backward_kernel(int P, int Wq, int Hq, const float* __restrict__ m
             float4 v = ga[i];
             a[4 * i] = v.x; a[4 * i + 1] = v.y; a[4 * i + 2] = v.z; a[4 * i + 3] = v.w;
         }
-        float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
-        float4 rot = rotations[idx];
-        float2 scale = scales[idx];
-        SbMat3 R = sb_quat_to_rotmat(rot);
-        SbMat3 S = sb_scale_to_mat(scale, 1.0f);
-        SbMat3 L = sb_mul33(R, S);
-        SbMat4x3 MT = sb_splat2world_T(L, p_orig);
-        SbMat4 world2ndc = sb_world2ndc(s_pm);
-        SbMat3x4 ndc2pix = sb_ndc2pix(Wq, Hq);
-        SbMat3x4 Pm = sb_mul44_34(world2ndc, ndc2pix);  // backward associates (world2ndc*ndc2pix) first, :909-910
-        SbMat3 T = sb_mul43_34(MT, Pm);
-        float3 l2 = {L.c[2][0], L.c[2][1], L.c[2][2]};
-        float3 normal = sb_transform_vec4x3(l2, s_vm);
+        float4 rot = {1.f, 0.f, 0.f, 0.f};
+        float2 scale = {0.f, 0.f};
+        SbMat3 R, T;
+        SbMat3x4 Pm;
+        float3 normal = {0.f, 0.f, 0.f};
+        if (PRECOMP) {
+#pragma unroll
+            for (int c = 0; c < 3; c++)
+#pragma unroll
+                for (int r = 0; r < 3; r++) T.c[c][r] = transmat_precomp[9 * (size_t)idx + 3 * c + r];
+        } else {
+            float3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+            rot = rotations[idx];
+            scale = scales[idx];
+            R = sb_quat_to_rotmat(rot);
+            SbMat3 S = sb_scale_to_mat(scale, 1.0f);
+            SbMat3 L = sb_mul33(R, S);
+            SbMat4x3 MT = sb_splat2world_T(L, p_orig);
+            SbMat4 world2ndc = sb_world2ndc(s_pm);
+            SbMat3x4 ndc2pix = sb_ndc2pix(Wq, Hq);
+            Pm = sb_mul44_34(world2ndc, ndc2pix);  // backward associates (world2ndc*ndc2pix) first, :909-910
+            T = sb_mul43_34(MT, Pm);
+            float3 l2 = {L.c[2][0], L.c[2][1], L.c[2][2]};
+            normal = sb_transform_vec4x3(l2, s_vm);
+        }
 
         SbMat3 dL_dT;
 #pragma unroll
@@ -104,30 +121,38 @@ sb_preprocess_backward_kernel(int P, int Wq, int Hq, const float* __restrict__ m
             dL_dT.c[2][1] += g2.x * dpx_dT31 + g2.y * dpy_dT31;
             dL_dT.c[2][2] += g2.x * dpx_dT32 + g2.y * dpy_dT32;
         }
-        // dL_dM = P * transpose(dL_dT)   (mat3x4 * mat3 -> mat3x4), :965
-        float dL_dM[3][4];
+        if (PRECOMP) {
+            // the (possibly updated) dL/dT is the output; the heuristic below reads it back (:950-961,1043-1044)
 #pragma unroll
-        for (int c = 0; c < 3; c++)
+            for (int c = 0; c < 3; c++)
 #pragma unroll
-            for (int r = 0; r < 4; r++)
-                dL_dM[c][r] = Pm.c[0][r] * dL_dT.c[0][c] + Pm.c[1][r] * dL_dT.c[1][c] + Pm.c[2][r] * dL_dT.c[2][c];
-        float3 dLn = {a[11], a[12], a[13]};
-        float3 dL_dtn = sb_transform_vec4x3_transpose(dLn, s_vm);
-        float multiplier = normal.z < 0 ? 1 : -1;
-        dL_dtn.x = multiplier * dL_dtn.x;
-        dL_dtn.y = multiplier * dL_dtn.y;
-        dL_dtn.z = multiplier * dL_dtn.z;
-        SbMat3 dL_dR;
+                for (int r = 0; r < 3; r++) a[3 * c + r] = dL_dT.c[c][r];
+        } else {
+            // dL_dM = P * transpose(dL_dT)   (mat3x4 * mat3 -> mat3x4), :965
+            float dL_dM[3][4];
 #pragma unroll
-        for (int r = 0; r < 3; r++) {
-            dL_dR.c[0][r] = dL_dM[0][r] * scale.x;
-            dL_dR.c[1][r] = dL_dM[1][r] * scale.y;
+            for (int c = 0; c < 3; c++)
+#pragma unroll
+                for (int r = 0; r < 4; r++)
+                    dL_dM[c][r] = Pm.c[0][r] * dL_dT.c[0][c] + Pm.c[1][r] * dL_dT.c[1][c] + Pm.c[2][r] * dL_dT.c[2][c];
+            float3 dLn = {a[11], a[12], a[13]};
+            float3 dL_dtn = sb_transform_vec4x3_transpose(dLn, s_vm);
+            float multiplier = normal.z < 0 ? 1 : -1;
+            dL_dtn.x = multiplier * dL_dtn.x;
+            dL_dtn.y = multiplier * dL_dtn.y;
+            dL_dtn.z = multiplier * dL_dtn.z;
+            SbMat3 dL_dR;
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                dL_dR.c[0][r] = dL_dM[0][r] * scale.x;
+                dL_dR.c[1][r] = dL_dM[1][r] * scale.y;
+            }
+            dL_dR.c[2][0] = dL_dtn.x; dL_dR.c[2][1] = dL_dtn.y; dL_dR.c[2][2] = dL_dtn.z;
+            o_rot = sb_quat_to_rotmat_vjp(rot, dL_dR);
+            o_scale.x = dL_dM[0][0] * R.c[0][0] + dL_dM[0][1] * R.c[0][1] + dL_dM[0][2] * R.c[0][2];
+            o_scale.y = dL_dM[1][0] * R.c[1][0] + dL_dM[1][1] * R.c[1][1] + dL_dM[1][2] * R.c[1][2];
+            o_mean3D = make_float3(dL_dM[2][0], dL_dM[2][1], dL_dM[2][2]);
         }
-        dL_dR.c[2][0] = dL_dtn.x; dL_dR.c[2][1] = dL_dtn.y; dL_dR.c[2][2] = dL_dtn.z;
-        o_rot = sb_quat_to_rotmat_vjp(rot, dL_dR);
-        o_scale.x = dL_dM[0][0] * R.c[0][0] + dL_dM[0][1] * R.c[0][1] + dL_dM[0][2] * R.c[0][2];
-        o_scale.y = dL_dM[1][0] * R.c[1][0] + dL_dM[1][1] * R.c[1][1] + dL_dM[1][2] * R.c[1][2];
-        o_mean3D = make_float3(dL_dM[2][0], dL_dM[2][1], dL_dM[2][2]);
         // densification heuristic replaces the screen-space gradient (Q9, :1041-1044); uses the raw
         // accumulated dL/dTu.z, dL/dTv.z and the *forward* Tw.z
         const float depth = rec[(size_t)idx * SB_REC_F4 + SB_REC_TW].z;
@@ -171,7 +196,8 @@ __global__ void sb_adam_kernel(float* __restrict__ param, const float* __restric
 }
 
 int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanfovy, const float* means3D,
-                                  const float* scales, const float* rotations, const float* viewmatrix,
+                                  const float* scales, const float* rotations, const float* transmat_precomp,
+                                  const float* viewmatrix,
                                   const float* projmatrix, const int* radii, const char* geom, const float* grad_acc,
                                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity,
                                   float* dL_dscales, float* dL_drotations, float* dL_dtransMat, float* scores,
@@ -185,8 +211,9 @@ int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanf
     volatile float fy2 = focal_y * tanfovy;
     const int Wq = int(fx2 * 2);
     const int Hq = int(fy2 * 2);
-    sb_preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, s>>>(
-        P, Wq, Hq, means3D, (const float2*)scales, (const float4*)rotations, viewmatrix, projmatrix, radii,
+    auto kern = transmat_precomp ? sb_preprocess_backward_kernel<true> : sb_preprocess_backward_kernel<false>;
+    kern<<<(P + 255) / 256, 256, 0, s>>>(
+        P, Wq, Hq, means3D, (const float2*)scales, (const float4*)rotations, transmat_precomp, viewmatrix, projmatrix, radii,
         (const float4*)geom, grad_acc, dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity, (float2*)dL_dscales,
         (float4*)dL_drotations, dL_dtransMat, (float2*)scores);
     sb_count_launch(1);

@@ -64,6 +64,14 @@ def _load():
     lib.sb200_forward_async.argtypes = [_i32, _i32, _i32] + [_vp] * 8 + [_vp, _vp, _vp, _i64] + [_vp] * 6
     lib.sb200_forward_wait.restype = _i32
     lib.sb200_forward_wait.argtypes = []
+    lib.sb200_forward_begin_precomp.restype = _i32
+    lib.sb200_forward_begin_precomp.argtypes = [_i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp, _vp, _vp]
+    lib.sb200_backward_precomp.restype = _i32
+    lib.sb200_backward_precomp.argtypes = [_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 22
+    lib.sb200_sh_forward.restype = _i32
+    lib.sb200_sh_forward.argtypes = [_i32, _i32, _i32] + [_vp] * 6
+    lib.sb200_sh_backward.restype = _i32
+    lib.sb200_sh_backward.argtypes = [_i32, _i32, _i32] + [_vp] * 9
     lib.sb200_backward.restype = _i32
     lib.sb200_backward.argtypes = [_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 24
     lib.sb200_mark_visible.restype = _i32
@@ -92,7 +100,7 @@ def _load():
     lib.sb200_prune_scratch_bytes.argtypes = [_i64]
     lib.sb200_prune_rows.restype = _i32
     lib.sb200_prune_rows.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp]
-    if lib.sb200_abi_version() != 5:
+    if lib.sb200_abi_version() != 6:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -166,10 +174,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         rs = raster_settings
         if means3D.ndim != 2 or means3D.size(1) != 3:
             raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:63-65
-        if sh is not None and sh.numel() != 0:
-            raise NotImplementedError("SH colours are not on VINGS-Mono's path (sh_degree=0, colors_precomp); Q16")
-        if cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0:
-            raise NotImplementedError("transMat_precomp is not on VINGS-Mono's path; Q16")
+        use_sh = sh is not None and sh.numel() != 0
+        if use_sh and (sh.ndim != 3 or sh.size(0) != means3D.size(0) or sh.size(2) != 3):
+            raise RuntimeError("shs must have dimensions (num_points, coefficients, 3)")
+        use_pre = cov3Ds_precomp is not None and cov3Ds_precomp.numel() != 0
+        if use_pre and cov3Ds_precomp.numel() != 9 * means3D.size(0):
+            raise RuntimeError("cov3D_precomp (transMat_precomp) must have dimensions (num_points, 9)")
         P = means3D.size(0)
         H, W = int(rs.image_height), int(rs.image_width)
         dev = means3D.device
@@ -177,8 +187,22 @@ class _RasterizeGaussians(torch.autograd.Function):
                          for t in (means3D, means2D, sh, colors_precomp, opacities, scales, rotations, scores,
                                    cov3Ds_precomp)] + [None]
         means3D = _f32c(means3D, "means3D")
-        colors = _f32c(colors_precomp, "colors_precomp")
+        ctx.use_sh = use_sh and P > 0
+        sh_c = clamped = campos = None
+        if ctx.use_sh:
+            # SH -> RGB as a stage in front of the rasterizer (reference: inside preprocessCUDA, forward.cu:237-242)
+            sh_c = _f32c(sh, "shs")
+            campos = _f32c(rs.campos, "campos")
+            colors = torch.empty((P, 3), dtype=torch.float32, device=dev)
+            clamped = torch.empty((P, 3), dtype=torch.uint8, device=dev)
+            _check(lib.sb200_sh_forward(P, int(rs.sh_degree), sh_c.size(1), _ptr(means3D), _ptr(campos), _ptr(sh_c),
+                                        _ptr(colors), _ptr(clamped), _stream(dev)), "sb200_sh_forward")
+        else:
+            colors = _f32c(colors_precomp, "colors_precomp")
         opac = _f32c(opacities, "opacities")
+        ctx.use_pre = use_pre and P > 0
+        # with a precomputed transform the reference's scales / rotations are empty tensors (__init__.py:216-222)
+        tm_c = _f32c(cov3Ds_precomp, "cov3D_precomp") if ctx.use_pre else None
         scales_c = _f32c(scales, "scales")
         rot_c = _f32c(rotations, "rotations")
         bg = _f32c(rs.bg, "bg")
@@ -200,9 +224,14 @@ class _RasterizeGaussians(torch.autograd.Function):
         geom = torch.empty(lib.sb200_geom_bytes(P), dtype=torch.uint8, device=dev)
         image = torch.empty(lib.sb200_image_bytes(W, H), dtype=torch.uint8, device=dev)
         count = _count_buffer(dev)
-        _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac), _ptr(colors),
-                                       _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii), _vp(count.data_ptr()),
-                                       stream), "sb200_forward_begin")
+        if ctx.use_pre:
+            _check(lib.sb200_forward_begin_precomp(P, W, H, _ptr(means3D), _ptr(tm_c), _ptr(opac), _ptr(colors),
+                                                   _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii),
+                                                   _vp(count.data_ptr()), stream), "sb200_forward_begin_precomp")
+        else:
+            _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac),
+                                           _ptr(colors), _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii),
+                                           _vp(count.data_ptr()), stream), "sb200_forward_begin")
         R = int(count[0])
         last_counters.update(P=P, R=R, W=W, H=H)
         # sort scratch is dead after the forward; only the sorted id list is kept for the backward
@@ -214,7 +243,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = rs
         ctx.P = P
         ctx.num_rendered = R
-        ctx.save_for_backward(means3D, scales_c, rot_c, radii, geom, point_list, image, color, others)
+        ctx.sh_degree = int(rs.sh_degree)
+        ctx.save_for_backward(means3D, tm_c if ctx.use_pre else scales_c, rot_c, radii, geom, point_list, image, color,
+                              others, *((sh_c, clamped, campos) if ctx.use_sh else ()))
         ctx.mark_non_differentiable(radii)
         return color, radii, others
 
@@ -229,7 +260,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             return tuple(torch.zeros(sh_, dtype=torch.float32, device=dev)
                          if sh_ is not None and ctx.needs_input_grad[i] else None
                          for i, sh_ in enumerate(ctx.in_shapes))
-        means3D, scales_c, rot_c, radii, geom, point_list, image, color, others = ctx.saved_tensors
+        means3D, scales_c, rot_c, radii, geom, point_list, image, color, others = ctx.saved_tensors[:9]
         dev = means3D.device
         g_color = _f32c(grad_out_color, "grad_out_color")
         g_others = _f32c(grad_depth, "grad_allmap")
@@ -248,15 +279,28 @@ class _RasterizeGaussians(torch.autograd.Function):
         dmeans3D, dmeans2D, dcolors, dopac = e(P, 3), e(P, 3), e(P, 3), e(P, 1)
         dscales, drot, dtrans, scores = e(P, 2), e(P, 4), e(P, 9), e(P, 2)
         grad_ws = torch.empty(lib.sb200_grad_bytes(P), dtype=torch.uint8, device=dev)
-        _check(lib.sb200_backward(P, W, H, ctx.num_rendered, _ptr(bg), float(rs.tanfovx), float(rs.tanfovy),
-                                  _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(view), _ptr(proj), _ptr(radii),
-                                  _ptr(geom), _ptr(point_list), _ptr(image), _ptr(color), _ptr(others),
-                                  _ptr(g_color), _ptr(g_others), _ptr(mask), _ptr(grad_ws),
-                                  _ptr(dmeans3D), _ptr(dmeans2D), _ptr(dcolors), _ptr(dopac), _ptr(dscales),
-                                  _ptr(drot), _ptr(dtrans), _ptr(scores), _stream(dev)), "sb200_backward")
+        tail = (_ptr(view), _ptr(proj), _ptr(radii), _ptr(geom), _ptr(point_list), _ptr(image), _ptr(color),
+                _ptr(others), _ptr(g_color), _ptr(g_others), _ptr(mask), _ptr(grad_ws), _ptr(dmeans3D), _ptr(dmeans2D),
+                _ptr(dcolors), _ptr(dopac), _ptr(dscales), _ptr(drot), _ptr(dtrans), _ptr(scores), _stream(dev))
+        if ctx.use_pre:  # scales_c holds the precomputed transforms
+            _check(lib.sb200_backward_precomp(P, W, H, ctx.num_rendered, _ptr(bg), float(rs.tanfovx),
+                                              float(rs.tanfovy), _ptr(scales_c), *tail), "sb200_backward_precomp")
+        else:
+            _check(lib.sb200_backward(P, W, H, ctx.num_rendered, _ptr(bg), float(rs.tanfovx), float(rs.tanfovy),
+                                      _ptr(means3D), _ptr(scales_c), _ptr(rot_c), *tail), "sb200_backward")
         # forward-argument order of the reference (__init__.py:156-167).  The reference hands a tensor to
         # every slot; autograd rejects that for inputs that were None, so those slots get None here.
-        grads = [dmeans3D, dmeans2D, None, dcolors, dopac, dscales, drot, scores, None, None]
+        dsh = None
+        if ctx.use_sh:
+            # dL/dcolors -> dL/dsh, plus the view-direction term of dL/dmeans3D (backward.cu:1038-1039)
+            sh_c, clamped, campos = ctx.saved_tensors[9:]
+            dsh = torch.empty_like(sh_c)
+            _check(lib.sb200_sh_backward(P, ctx.sh_degree, sh_c.size(1), _ptr(means3D), _ptr(campos), _ptr(sh_c),
+                                         _ptr(clamped), _ptr(radii), _ptr(dcolors), _ptr(dmeans3D), _ptr(dsh),
+                                         _stream(dev)), "sb200_sh_backward")
+        # slot 8 = cov3Ds_precomp: the reference returns dL/dtransMat there (__init__.py:165)
+        grads = [dmeans3D, dmeans2D, dsh, None if ctx.use_sh else dcolors, dopac, dscales, drot, scores,
+                 dtrans if ctx.use_pre else None, None]
         for i, shape in enumerate(ctx.in_shapes):
             if shape is None or not ctx.needs_input_grad[i]:
                 grads[i] = None
