@@ -124,6 +124,7 @@ sb_pair_offsets_kernel(const uint32_t* __restrict__ sorted_ids, const uint32_t* 
 }
 
 #define DUP_THREADS 256
+static_assert(SB_EMIT_CHUNK / DUP_THREADS == 4, "the duplicate kernel emits 4 pairs per thread");
 #define DUP_WINDOW (SB_EMIT_CHUNK + DUP_THREADS)  // a chunk of n pairs starts in at most n surfels
 
 // dynamic shared memory: uint32 s_hist[hist_words] (tile counts of this CTA; 0 words = count with global REDs)
@@ -165,25 +166,46 @@ sb_duplicate_kernel(uint32_t grid_x, int64_t R, const unsigned long long* __rest
             // the last surfel loaded so far (thread 255's) decides whether the window is complete
             if (__syncthreads_or(tid == DUP_THREADS - 1 && o >= end) || n >= DUP_WINDOW) break;
         }
-        // ---- every pair finds its surfel: first k with s_incl[k] > j ----
-#pragma unroll
-        for (int m = 0; m < SB_EMIT_CHUNK / DUP_THREADS; m++) {
-            const uint32_t j = begin + m * DUP_THREADS + tid;
-            if (j < end) {
+        // ---- every thread takes 4 consecutive pairs: one binary search (first k with s_incl[k] > j) for the first,
+        // the others step forward from it; the 4 (tile, id) results leave as one 128-bit store each ----
+        {
+            constexpr int PER = SB_EMIT_CHUNK / DUP_THREADS;
+            const uint32_t j0 = begin + PER * tid;
+            uint32_t tk[PER], tv[PER];
+            if (j0 < end) {
                 int lo = 0, len = n;
                 while (len > 0) {
                     const int half = len >> 1;
-                    if (s_incl[lo + half] <= j) { lo += half + 1; len -= half + 1; } else { len = half; }
+                    if (s_incl[lo + half] <= j0) { lo += half + 1; len -= half + 1; } else { len = half; }
                 }
-                const uint32_t excl = lo ? s_incl[lo - 1] : base_excl;
-                const uint32_t t = j - excl;
-                const uint32_t rw = s_rw[lo], rmin = s_rmin[lo];
-                const uint32_t ty = t / rw, tx = t - ty * rw;
-                const uint32_t tile = ((rmin >> 16) + ty) * grid_x + (rmin & 0xffffu) + tx;
-                keys[j] = tile;
-                vals[j] = s_id[lo];
-                if (hist_words) atomicAdd(&s_hist[tile], 1u);
-                else atomicAdd(tile_counts + tile, 1u);
+                uint32_t excl = lo ? s_incl[lo - 1] : base_excl;
+                uint32_t incl = s_incl[lo], rw = s_rw[lo], rmin = s_rmin[lo], id = s_id[lo];
+#pragma unroll
+                for (int m = 0; m < PER; m++) {
+                    const uint32_t j = j0 + m;
+                    tk[m] = 0; tv[m] = 0;
+                    if (j < end) {
+                        while (j >= incl) {  // next surfel (every staged surfel owns at least one pair)
+                            lo++;
+                            excl = incl;
+                            incl = s_incl[lo]; rw = s_rw[lo]; rmin = s_rmin[lo]; id = s_id[lo];
+                        }
+                        const uint32_t t = j - excl;
+                        const uint32_t ty = t / rw, tx = t - ty * rw;
+                        const uint32_t tile = ((rmin >> 16) + ty) * grid_x + (rmin & 0xffffu) + tx;
+                        tk[m] = tile; tv[m] = id;
+                        if (hist_words) atomicAdd(&s_hist[tile], 1u);
+                        else atomicAdd(tile_counts + tile, 1u);
+                    }
+                }
+                if (j0 + PER <= end) {  // chunk starts are multiples of 1024: 16-byte aligned
+                    *reinterpret_cast<uint4*>(keys + j0) = make_uint4(tk[0], tk[1], tk[2], tk[3]);
+                    *reinterpret_cast<uint4*>(vals + j0) = make_uint4(tv[0], tv[1], tv[2], tv[3]);
+                } else {
+#pragma unroll
+                    for (int m = 0; m < PER; m++)
+                        if (j0 + m < end) { keys[j0 + m] = tk[m]; vals[j0 + m] = tv[m]; }
+                }
             }
         }
     }
