@@ -177,7 +177,7 @@ def cpu_baseline():
                       "of the pure-torch CPU emulation; the mapping-step config itself is out of reach on CPU"}
 
 
-def main():
+def run(emit):
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -200,7 +200,7 @@ def main():
         mod = load_module(args.impl)
     except RuntimeError as e:
         if args.impl == "reference":
-            print(json.dumps({"impl": "reference", "unavailable": str(e)}))
+            emit(json.dumps({"impl": "reference", "unavailable": str(e)}))
             return 0
         raise
     cfg = synthetic.CONFIGS[args.config]
@@ -433,10 +433,28 @@ def main():
     if mine and rank == 0 and world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline()
     if rank == 0:
-        print(json.dumps(out))
+        emit(json.dumps(out))
     if world > 1:
         torch.distributed.destroy_process_group()
     return 0
+
+
+def main():
+    """stdout carries the ONE JSON line and nothing else: while the bench runs, file descriptor 1 points at stderr, so
+    what libraries print there (NCCL's version banner on communicator creation) cannot precede the line."""
+    lines = []
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        rc = run(lines.append)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    for ln in lines:
+        print(ln, flush=True)
+    return rc
 
 
 if __name__ == "__main__":
