@@ -105,6 +105,10 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+SHAPE_NAMES = {"C1": "small synthetic", "C2": "KITTI-shaped", "C3": "RTG Hotel-shaped indoor",
+               "C4": "Hierarchical SmallCity-shaped", "C5": "Waymo-shaped 5-camera"}
+
+
 def load_module(impl):
     if impl == "reference":
         import util
@@ -333,8 +337,9 @@ def run(emit):
         "value": value, "unit": "views/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_val / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "%s: KITTI-shaped mapping step, %d surfels, %d-keyframe window at %dx%d, %s loss; "
-                               "one step = %d views per rank" % (args.config, P, K, W, H, cfg["sup"], VIEWS_PER_STEP),
+        "config": {"workload": "%s: %s mapping step, %d surfels, %d-keyframe window at %dx%d, %s loss; "
+                               "one step = %d views per rank" % (args.config, SHAPE_NAMES.get(args.config, "synthetic"),
+                                                                 P, K, W, H, cfg["sup"], VIEWS_PER_STEP),
                    "mapping_step": "fused (activate, rasterizer, map_loss, surfel_update kernels)" if mapper.fused
                                    else "torch autograd + torch loss around the rasterizer module",
                    "surfels": P, "window": K, "width": W, "height": H, "views_per_step_per_rank": VIEWS_PER_STEP,
