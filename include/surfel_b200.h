@@ -106,10 +106,12 @@ int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg /* [3] 
 
 /* Both stages in one call WITHOUT a host synchronisation, for callers that keep a binning scratch of
  * `pair_capacity` pairs (sb200_binning_bytes(pair_capacity), point_list[pair_capacity]): every launch takes the
- * pair count from device memory.  R is copied to *num_rendered_host (pinned host memory) right after the
- * preprocess; sb200_forward_wait() blocks until that copy of the calling thread's most recent forward_async on the
- * current device has landed - call it wherever convenient before committing the view's results (the mapper
- * does just before its parameter update, with the rest of the view already queued, so the GPU never idles).
+ * pair count from device memory.  R is copied to *num_rendered_host (pinned host memory, owned by the caller's
+ * workspace) right after the preprocess and `sync` (a handle from sb200_sync_create, one per workspace) is recorded
+ * behind that copy; sb200_forward_wait(sync) blocks until the copy has landed - call it wherever convenient before
+ * committing the view's results (the mapper does just before its parameter update, with the rest of the view
+ * already queued, so the GPU never idles).  Count buffer and handle belong to ONE workspace: forwards of other
+ * workspaces, streams or threads in between do not disturb them (re-entrant per workspace).
  * If R > pair_capacity only the first pair_capacity pairs (depth order) were binned: the outputs are memory-safe
  * but wrong, and the caller must grow the scratch and run the forward again.  Pass pair_capacity (not R) as R to
  * sb200_backward. */
@@ -117,8 +119,11 @@ int sb200_forward_async(int P, int W, int H, const float* means3D, const float* 
                         const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
                         const float* bg, void* geom_ws, int* radii, void* binning_ws, int64_t pair_capacity,
                         uint32_t* point_list, void* image_ws, float* out_color, float* out_others,
-                        int64_t* num_rendered_host, void* stream);
-int sb200_forward_wait(void);
+                        int64_t* num_rendered_host, void* sync, void* stream);
+int sb200_forward_wait(void* sync);
+/* hand-off handles of sb200_forward_async (a CUDA event of the current device); NULL on failure */
+void* sb200_sync_create(void);
+void sb200_sync_destroy(void* sync);
 
 /* ---- backward ------------------------------------------------------------------------------- */
 /* All dL_d* outputs and scores are fully written (no pre-zeroing needed).  dL_dtransMat may be NULL.
@@ -247,6 +252,14 @@ int sb200_sh_backward(int P, int degree, int n_coeffs, const float* means3D, con
  * keys equal to 0xFFFFFFFF are dropped, *n_valid_dev (device u32) receives the number of pairs kept. */
 int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, int mode, uint32_t* vals_out, uint32_t* n_valid_dev,
                      void* stream);
+
+/* Test hook for reference quirk Q17: the reference's forward stores a per-tile `max_contrib`
+ * (cuda_rasterizer/forward.cu:496-502) that its backward uses to drop whole 32-surfel buckets (backward.cu:503-505),
+ * and that value is not the tile maximum (cub::BlockReduce<.,256> on a 16x16 block).  With per_tile_cap (device
+ * u32[tiles], must stay alive) set, the calling thread's following sb200_backward calls stop every tile's walk at
+ * ceil(cap/32) buckets exactly like the reference does, which lets a test show that this quirk explains ALL of the
+ * gradient difference on the surfels it excludes.  NULL switches it off (the default). */
+int sb200_debug_walk_cap(const uint32_t* per_tile_cap);
 
 #ifdef __cplusplus
 }

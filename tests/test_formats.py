@@ -94,3 +94,30 @@ def test_pt_checkpoint_round_trip_restores_mapper(tmp_path):
     with pytest.raises(KeyError):
         torch.save({"_xyz": m._xyz}, path)
         formats.load_pt_ckpt(path)
+
+
+def test_pt_ckpt_holds_exactly_P_rows(tmp_path):
+    """In fused mode the mapper's attributes are [:P] views into capacity-sized store buffers; the checkpoint must
+    hold P rows, not the capacity (torch.save serialises a view's whole storage)."""
+    class FakeMapper:
+        pass
+    m = FakeMapper()
+    cap, P = 200_000, 1_000
+    cols = dict(_xyz=3, _rgb=3, _opacity=1, _scaling=2, _rotation=4, _local_scores=2, _global_scores=2)
+    for k in formats.GROUPS + formats.BOOK:
+        if k == "_stable_mask":
+            big = torch.zeros(cap, dtype=torch.bool)
+        elif k == "_globalkf_id":
+            big = torch.arange(cap, dtype=torch.long)
+        elif k == "_globalkf_max_scores":
+            big = torch.rand(cap)
+        else:
+            big = torch.randn(cap, cols[k])
+        setattr(m, k, big[:P])
+    path = str(tmp_path / "views.pt")
+    formats.save_pt_ckpt(m, path)
+    assert os.path.getsize(path) < 4 * P * (15 + 2 + 2 + 1 + 2 + 1) * 4   # ~P rows of every array, not `cap`
+    d = formats.load_pt_ckpt(path)
+    for k in formats.GROUPS + formats.BOOK:
+        assert torch.equal(d[k], getattr(m, k)), k
+        assert d[k].untyped_storage().nbytes() == d[k].numel() * d[k].element_size(), k

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
     assert len(names) >= 15
     for n in sorted(names):
         assert hasattr(lib, n), n
-    assert lib.sb200_abi_version() == 6
+    assert lib.sb200_abi_version() == 7
     assert lib.sb200_last_error() == b""
 
 

@@ -156,50 +156,35 @@ def test_activate_matches_torch():
     assert torch.allclose(ar, torch.nn.functional.normalize(r), rtol=1e-6, atol=1e-7)
 
 
-def _mapper_pair(mine, sup, P=20000, n_views=3, stable_frac=0.1):
+@pytest.mark.gpu
+@pytest.mark.parametrize("sup", ["rgb+depth", "rgb+depth+normal+dist"])
+def test_fused_view_matches_torch_view(sup):
+    """Three training views: torch autograd + torch loss + 5 Adam launches vs the fused path, ONE step at a time
+    from bit-identical state (util.sync_mapper_state; see there why trajectories are not compared)."""
+    mine = util.load_mine()
+    P = 20000
     scene, views = synthetic.make_scene("C3", P=P, W=160, H=96)
     dev = torch.device("cuda")
     a = mapper_step.SurfelMapper(mine, scene, dev, supervision=sup, fused=False)
     b = mapper_step.SurfelMapper(mine, scene, dev, supervision=sup, fused=True)
     g = torch.Generator(device="cpu").manual_seed(1)
-    stable = (torch.rand(P, generator=g) < stable_frac).cuda()
-    a._stable_mask, b._stable_mask = stable.clone(), stable.clone()
+    stable = (torch.rand(P, generator=g) < 0.1).cuda()
+    a._stable_mask = stable.clone()
+    b._stable_mask.copy_(stable)
     init = {k: getattr(a, k).data.clone() for k in mapper_step.GROUPS}
-    losses = []
-    for i in range(n_views):
+    for i in range(3):
         v = views[-1 - (i % len(views))]
         gt = {k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()}
         vd = mapper_step.view_to_device(v, dev)
-        losses.append((float(a.train_view(vd, gt, kf_id=i + 1)), float(b.train_view(vd, gt, kf_id=i + 1))))
-    return a, b, losses, init
-
-
-@pytest.mark.gpu
-@pytest.mark.parametrize("sup", ["rgb+depth", "rgb+depth+normal+dist"])
-def test_fused_view_matches_torch_view(sup):
-    """Three training views from the same start: torch autograd + torch loss + 5 Adam launches vs the fused
-    path.  Parameters move by lr-sized steps whose direction is sign-like (Adam), so moments and scores are the
-    sensitive quantities."""
-    mine = util.load_mine()
-    a, b, losses, init = _mapper_pair(mine, sup)
-    for la, lb in losses:
-        assert abs(la - lb) <= 2e-5 * max(1.0, abs(la)), losses
+        la, lb = float(a.train_view(vd, gt, kf_id=i + 1)), float(b.train_view(vd, gt, kf_id=i + 1))
+        assert abs(la - lb) <= 2e-5 * max(1.0, abs(la)), (i, la, lb)
+        util.assert_one_step_agrees(a, b, ctx="%s view %d" % (sup, i))
+        util.sync_mapper_state(a, b)
     for k in mapper_step.GROUPS:
-        pa, pb = getattr(a, k).data, getattr(b, k).data
-        sa, sb = a.optimizer.state[getattr(a, k)], b.optimizer.state[getattr(b, k)]
-        assert util.rel_err(sb["exp_avg"], sa["exp_avg"]) < 2e-3, (k, util.rel_err(sb["exp_avg"], sa["exp_avg"]))
-        assert util.rel_err(sb["exp_avg_sq"], sa["exp_avg_sq"]) < 2e-3, k
-        assert float((pa - init[k]).abs().sum()) > 0, k
-        assert float((pa - pb).abs().max()) <= 2.5 * mapper_step.LR[k] * 3, (k, float((pa - pb).abs().max()))
-        assert util.rel_err(pb, pa) < 1e-5, k
-    assert util.rel_err(b._local_scores, a._local_scores) < 1e-4
-    assert util.rel_err(b._global_scores, a._global_scores) < 1e-4
-    assert util.rel_err(b._globalkf_max_scores, a._globalkf_max_scores) < 1e-4
-    assert float((a._globalkf_id != b._globalkf_id).float().mean()) < 1e-3
+        assert float((getattr(b, k).data - init[k]).abs().sum()) > 0, k
     # surfels frozen by _stable_mask did not move
-    st = a._stable_mask
-    assert torch.equal(b._xyz.data[st], init["_xyz"][st])
-    assert not torch.equal(b._xyz.data[~st], init["_xyz"][~st])
+    assert torch.equal(b._xyz.data[stable], init["_xyz"][stable])
+    assert not torch.equal(b._xyz.data[~stable], init["_xyz"][~stable])
 
 
 @pytest.mark.gpu

@@ -24,6 +24,7 @@ pytestmark = pytest.mark.gpu
 # this implementation reduces 32 pixels by shuffle, 8 warps through shared memory and tiles by atomics -- a
 # different, also nondeterministic, association.  Measured agreement: 5e-7 (C1) .. 7e-5 (C2) relative L1.
 GRAD_TOL = 5e-4
+TAINT_BOUND = 0.10   # share of the visible surfels quirk Q17 may exclude (measured 0 .. 4 %)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
@@ -97,6 +98,9 @@ def test_gradients_match_reference(mine, ref, name, kw):
     ids, nbad = util.tainted_surfels(ri, inp["W"], inp["H"])   # reference UB, quirk Q17
     keep = torch.ones(om["d_scores"].shape[0], dtype=torch.bool)
     keep[torch.from_numpy(ids)] = False
+    # the exclusion set (reference UB, Q17) is bounded; test_parity_full_gpu.py proves it is exactly right
+    V = int((orf["radii"] > 0).sum())
+    assert len(ids) <= TAINT_BOUND * max(V, 1), (len(ids), V, nbad)
     assert torch.equal(om["radii"], orf["radii"])
     for k in ("d_means3D", "d_means2D", "d_colors", "d_opacities", "d_scales", "d_rotations", "d_scores"):
         assert om[k].shape == orf[k].shape

@@ -242,3 +242,66 @@ def tainted_surfels(ri, W, H):
         ids.append(ri["point_list"][int(r0) + 32 * int(done[t]):int(r1)])
     ids = np.unique(np.concatenate(ids)) if ids else np.zeros(0, np.int64)
     return ids.astype(np.int64), len(bad)
+
+
+def sync_mapper_state(dst, src):
+    """Copy parameters, Adam moments and score bookkeeping of mapper `src` into mapper `dst` (same surfel count).
+
+    Trajectory tests compare two implementations of the mapping step (fused kernels vs torch autograd).  Gradient
+    sums differ by atomic-order jitter between ANY two runs, and Adam's m / sqrt(v) normalisation amplifies that
+    from step to step, so a bound on "loss after k steps" is a bound on chaos, not on the code.  The tests therefore
+    re-synchronise the two mappers after every step and compare ONE step from bit-identical state: the loss then
+    depends only on the (deterministic, atomics-free) forward and on the loss kernel's summation order."""
+    import mapper_step
+    assert dst.P == src.P
+    with torch.no_grad():
+        for k in mapper_step.GROUPS:
+            pd, ps = getattr(dst, k), getattr(src, k)
+            pd.data.copy_(ps.data)
+            sd, ss = dst.optimizer.state[pd], src.optimizer.state[ps]
+            if len(ss) == 0:
+                assert len(sd) == 0 or float(sd["exp_avg"].abs().sum()) == 0.0
+                continue
+            if len(sd) == 0:   # a fresh torch-side optimizer: the other side's moments must be zeros too
+                assert float(ss["exp_avg"].abs().sum()) == 0.0 and float(ss["exp_avg_sq"].abs().sum()) == 0.0, k
+                continue
+            sd["exp_avg"].copy_(ss["exp_avg"])
+            sd["exp_avg_sq"].copy_(ss["exp_avg_sq"])
+        for name in dst.BOOK:
+            cur = getattr(dst, name)
+            new = getattr(src, name).detach().reshape(cur.shape).to(cur.dtype)
+            if dst.fused:
+                cur.copy_(new)   # views into the surfel store
+            else:
+                setattr(dst, name, new.clone())
+
+
+ADAM_STEP = (1.0 - 0.9) / (1.0 - 0.999) ** 0.5   # |m / sqrt(v)| = 3.16 after one step from zero moments (adam.cu:26-37)
+# Cauchy-Schwarz over the two exponential windows: |m| / sqrt(v) <= sqrt(sum_j (1-b1)^2 b1^2j / ((1-b2) b2^j)) = 7.3
+ADAM_RATIO_MAX = 7.3
+
+
+def assert_one_step_agrees(a, b, ctx=""):
+    """Mappers `a` and `b` took ONE training step from bit-identical state (sync_mapper_state) through different
+    implementations.  Their gradients agree to atomic-order jitter (<= GRAD_TOL relative L1, test_parity_gpu.py) plus
+    the fp32 summation order of the loss (2e-5), so:
+      * the moments, linear / quadratic in the gradient, agree to a few times that (2e-3 relative L1);
+      * a parameter element moves by at most ADAM_RATIO_MAX * lr per step, hence two paths differ by at most twice
+        that -- and only where the gradient's sign-like ratio m / sqrt(v) flips, i.e. where a gradient sum cancels to
+        ~5 digits: fewer than 1 element in 1000 may differ by more than 1 % of a first step (+ 2 ulp of the value)."""
+    import mapper_step
+    for k in mapper_step.GROUPS:
+        pa, pb = getattr(a, k).data, getattr(b, k).data
+        sa, sb = a.optimizer.state[getattr(a, k)], b.optimizer.state[getattr(b, k)]
+        assert rel_err(sb["exp_avg"], sa["exp_avg"]) < 2e-3, (ctx, k, rel_err(sb["exp_avg"], sa["exp_avg"]))
+        assert rel_err(sb["exp_avg_sq"], sa["exp_avg_sq"]) < 2e-3, (ctx, k, rel_err(sb["exp_avg_sq"], sa["exp_avg_sq"]))
+        lr = mapper_step.LR[k]
+        diff = (pa - pb).abs()
+        ulp2 = 2.5e-7 * pa.abs()
+        assert bool((diff <= 2.0 * ADAM_RATIO_MAX * lr + ulp2).all()), (ctx, k, float(diff.max()))
+        frac = float((diff > 0.01 * ADAM_STEP * lr + ulp2).float().mean())
+        assert frac < 1e-3, (ctx, k, frac)
+    assert rel_err(b._local_scores, a._local_scores) < 1e-4, ctx
+    assert rel_err(b._global_scores, a._global_scores) < 1e-4, ctx
+    assert rel_err(b._globalkf_max_scores, a._globalkf_max_scores) < 1e-4, ctx
+    assert float((a._globalkf_id != b._globalkf_id).float().mean()) < 1e-3, ctx

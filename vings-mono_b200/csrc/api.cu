@@ -58,7 +58,7 @@ void sb_set_error(const char* fmt, ...) {
 
 extern "C" {
 
-int sb200_abi_version(void) { return 6; }
+int sb200_abi_version(void) { return 7; }
 
 long long sb200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -238,14 +238,14 @@ int sb200_forward_async(int P, int W, int H, const float* means3D, const float* 
                         const float* opacities, const float* colors, const float* viewmatrix, const float* projmatrix,
                         const float* bg, void* geom_ws, int* radii, void* binning_ws, int64_t pair_capacity,
                         uint32_t* point_list, void* image_ws, float* out_color, float* out_others,
-                        int64_t* num_rendered_host, void* stream) {
+                        int64_t* num_rendered_host, void* sync, void* stream) {
     g_err[0] = 0;
     if (check_dims(P, W, H)) return 1;
     if (!num_rendered_host) { sb_set_error("num_rendered_host is NULL"); return 1; }
     if (pair_capacity < 1) { sb_set_error("forward_async: pair_capacity must be positive"); return 1; }
     cudaStream_t s = (cudaStream_t)stream;
-    cudaEvent_t ev = sync_event();
-    if (!ev) { sb_set_error("forward_async: no event"); return 2; }
+    cudaEvent_t ev = (cudaEvent_t)sync;
+    if (!ev) { sb_set_error("forward_async: sync handle is NULL (sb200_sync_create)"); return 1; }
     *num_rendered_host = 0;
     int rc;
     if (P > 0) {
@@ -272,12 +272,27 @@ int sb200_forward_async(int P, int W, int H, const float* means3D, const float* 
                                out_color, out_others, s);
 }
 
-int sb200_forward_wait(void) {
-    cudaEvent_t ev = sync_event();
-    if (!ev) { sb_set_error("forward_wait: no event"); return 2; }
-    SB_CUDA_CHECK(cudaEventSynchronize(ev));
+int sb200_forward_wait(void* sync) {
+    g_err[0] = 0;
+    if (!sync) { sb_set_error("forward_wait: sync handle is NULL"); return 1; }
+    SB_CUDA_CHECK(cudaEventSynchronize((cudaEvent_t)sync));
     return 0;
 }
+
+void* sb200_sync_create(void) {
+    g_err[0] = 0;
+    cudaEvent_t ev = nullptr;
+    cudaError_t e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+    if (e != cudaSuccess) { sb_set_error("sync_create: %s", cudaGetErrorString(e)); return nullptr; }
+    return (void*)ev;
+}
+
+void sb200_sync_destroy(void* sync) {
+    if (sync) cudaEventDestroy((cudaEvent_t)sync);
+}
+
+// test hook: per-tile cap of the backward walk for the calling thread's next backward calls (NULL = off)
+static thread_local const uint32_t* g_walk_cap = nullptr;
 
 static int backward_impl(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
                    const float* means3D, const float* scales, const float* rotations, const float* transmat,
@@ -303,7 +318,7 @@ static int backward_impl(int P, int W, int H, int64_t R, const float* bg, float 
         SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
         rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
                                       out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
-                                      (float*)grad_ws, s);
+                                      (float*)grad_ws, g_walk_cap, s);
         if (rc) return rc;
     } else {
         SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
@@ -338,6 +353,11 @@ int sb200_backward_precomp(int P, int W, int H, int64_t R, const float* bg, floa
                          projmatrix, radii, geom_ws, point_list, image_ws, out_color, out_others, dL_dout_color,
                          dL_dout_others, pixel_mask, grad_ws, dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dopacity,
                          dL_dscales, dL_drotations, dL_dtransMat, scores, stream);
+}
+
+int sb200_debug_walk_cap(const uint32_t* per_tile_cap) {
+    g_walk_cap = per_tile_cap;
+    return 0;
 }
 
 int sb200_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -89,7 +89,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                          const uint32_t* __restrict__ n_contrib, const float* __restrict__ out_color,
                          const float* __restrict__ out_others, const float* __restrict__ dL_dpixels,
                          const float* __restrict__ dL_dothers, const bool* __restrict__ pixel_mask,
-                         float* __restrict__ grad_acc) {
+                         float* __restrict__ grad_acc, const uint32_t* __restrict__ walk_cap) {
     __shared__ __align__(128) float4 s_rec[BB_STAGES][BB_BATCH][SB_REC_F4];
     __shared__ uint32_t s_id[BB_STAGES][BB_BATCH];
     __shared__ __align__(8) uint64_t s_full[BB_STAGES];
@@ -162,7 +162,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     uint32_t maxlast = 0;
 #pragma unroll
     for (int w = 0; w < BB_CWARPS; w++) maxlast = max(maxlast, s_maxlast[w]);
-    const int n_walk = min(n, (int)maxlast);
+    int n_walk = min(n, (int)maxlast);
+    // test hook (sb200_debug_walk_cap): stop where the reference's stored max_contrib makes ITS backward stop
+    // (whole 32-surfel buckets at or beyond it are dropped, backward.cu:503-505; quirk Q17 in DESIGN.md)
+    if (walk_cap) n_walk = min(n_walk, (int)((walk_cap[tile] + BB_BATCH - 1) / BB_BATCH) * BB_BATCH);
     const int nbatches = (n_walk + BB_BATCH - 1) / BB_BATCH;
 
     // gather the records of batch b into ring stage b % BB_STAGES (called by one whole warp)
@@ -441,13 +444,13 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                              const char* image, const float* out_color, const float* out_others,
                              const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
-                             float* grad_acc, cudaStream_t s) {
+                             float* grad_acc, const uint32_t* walk_cap, cudaStream_t s) {
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
     sb_blend_backward_kernel<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
-        dL_dcolor, dL_dothers, pixel_mask, grad_acc);
+        dL_dcolor, dL_dothers, pixel_mask, grad_acc, walk_cap);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

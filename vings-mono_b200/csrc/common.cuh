@@ -218,7 +218,7 @@ int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, con
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                              const char* image, const float* out_color, const float* out_others,
                              const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
-                             float* grad_acc, cudaStream_t s);
+                             float* grad_acc, const uint32_t* walk_cap, cudaStream_t s);
 int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanfovy, const float* means3D,
                                   const float* scales, const float* rotations, const float* transmat_precomp,
                                   const float* viewmatrix,

@@ -27,6 +27,7 @@
 //                            backward of the depth -> normal stencil as a gather (no atomics)
 //   sb_loss_final_kernel     the scalar
 #include "common.cuh"
+#include <mutex>
 
 #define ML_TX 32
 #define ML_TY 16
@@ -428,8 +429,13 @@ int sb_launch_map_loss(int W, int H, const float* color, const float* allmap, co
                        const float* gt_depth, const float* gt_cov, const float* w2c, float cx, float cy, float fx,
                        float fy, float w_rgb, float w_norm, float w_alpha, float w_depth, float w_dist, char* ws,
                        float* loss, float* dL_dcolor, float* dL_dallmap, cudaStream_t s) {
-    static bool gauss_ready = false;  // same constants for every call; uploaded once per process
-    if (!gauss_ready) {
+    // same constants for every call; constant memory is per device, so the upload is tracked per device
+    // (cudaMemcpyToSymbol writes the CURRENT device's copy only) and guarded for concurrent first calls
+    static std::mutex gauss_mu;
+    static bool gauss_ready_dev[SB_MAX_DEVICES] = {};
+    const int gdev = sb_current_device();
+    std::lock_guard<std::mutex> gauss_lock(gauss_mu);
+    if (!gauss_ready_dev[gdev]) {
         float g[11], sum = 0.f;
         for (int x = 0; x < 11; x++) {
             g[x] = (float)exp(-(double)((x - 5) * (x - 5)) / (2.0 * 1.5 * 1.5));
@@ -437,7 +443,7 @@ int sb_launch_map_loss(int W, int H, const float* color, const float* allmap, co
         }
         for (int x = 0; x < 11; x++) g[x] /= sum;
         SB_CUDA_CHECK(cudaMemcpyToSymbol(c_gauss, g, sizeof(g)));
-        gauss_ready = true;
+        gauss_ready_dev[gdev] = true;
     }
     const int HW = W * H;
     SbLossHeader* hdr = (SbLossHeader*)ws;

@@ -61,9 +61,13 @@ def _load():
     lib.sb200_forward_finish.restype = _i32
     lib.sb200_forward_finish.argtypes = [_i32, _i32, _i32, _i64] + [_vp] * 8
     lib.sb200_forward_async.restype = _i32
-    lib.sb200_forward_async.argtypes = [_i32, _i32, _i32] + [_vp] * 8 + [_vp, _vp, _vp, _i64] + [_vp] * 6
+    lib.sb200_forward_async.argtypes = [_i32, _i32, _i32] + [_vp] * 8 + [_vp, _vp, _vp, _i64] + [_vp] * 7
     lib.sb200_forward_wait.restype = _i32
-    lib.sb200_forward_wait.argtypes = []
+    lib.sb200_forward_wait.argtypes = [_vp]
+    lib.sb200_sync_create.restype = _vp
+    lib.sb200_sync_create.argtypes = []
+    lib.sb200_sync_destroy.restype = None
+    lib.sb200_sync_destroy.argtypes = [_vp]
     lib.sb200_forward_begin_precomp.restype = _i32
     lib.sb200_forward_begin_precomp.argtypes = [_i32, _i32, _i32] + [_vp] * 6 + [_vp, _vp, _vp, _vp]
     lib.sb200_backward_precomp.restype = _i32
@@ -80,6 +84,8 @@ def _load():
     lib.sb200_adam_update.argtypes = [_vp, _vp, _vp, _vp, _vp, _f32, _f32, _f32, _f32, _u32, _u32, _vp]
     lib.sb200_sort_pairs.restype = _i32
     lib.sb200_sort_pairs.argtypes = [_vp, _i64, _i32, _i32, _vp, _vp, _vp]
+    lib.sb200_debug_walk_cap.restype = _i32
+    lib.sb200_debug_walk_cap.argtypes = [_vp]
     lib.sb200_launch_count.restype = ctypes.c_longlong
     lib.sb200_profile_enable.restype = _i32
     lib.sb200_profile_enable.argtypes = [_i32]
@@ -100,7 +106,7 @@ def _load():
     lib.sb200_prune_scratch_bytes.argtypes = [_i64]
     lib.sb200_prune_rows.restype = _i32
     lib.sb200_prune_rows.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp]
-    if lib.sb200_abi_version() != 6:
+    if lib.sb200_abi_version() != 7:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
     return lib
@@ -128,17 +134,88 @@ def _f32c(t, name):
     return t.contiguous()
 
 
-# pinned 8-byte landing pad for the pair count, one per device
-_pinned_counts = {}
+class _Workspace:
+    """Buffers one forward -> backward pair of the drop-in path needs besides its outputs: geometry, image and
+    binning workspaces, the sorted id list, the gradient accumulation scratch, and the hand-off state of the
+    sync-free forward (pinned pair-count pad + event).  Pooled per (device, stream) and leased to an autograd node
+    for its lifetime, so a training loop allocates nothing per call after its second iteration (the reference
+    resizes four byte tensors per call through its allocator callbacks, rasterize_points.cu:32-38)."""
+
+    def __init__(self, device):
+        lib = _load()
+        self.device = device
+        self.geom = self.image = self.grad_ws = self.binning = None
+        self.point_list = None
+        self.geom_P = self.grad_P = 0
+        self.image_WH = None
+        self.pair_capacity = 0
+        self.count = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self.sync = lib.sb200_sync_create()
+        if not self.sync:
+            raise RuntimeError("sb200_sync_create failed: %s" % lib.sb200_last_error().decode())
+        self.busy = False
+
+    def __del__(self):
+        try:
+            if self.sync:
+                _load().sb200_sync_destroy(self.sync)
+                self.sync = None
+        except Exception:
+            pass
+
+    def fit(self, P, W, H):
+        lib = _load()
+        u8 = lambda n: torch.empty(n, dtype=torch.uint8, device=self.device)
+        if P > self.geom_P:   # the layouts are monotone in P: a larger buffer serves any smaller P
+            cap = max(P, int(self.geom_P * 1.25))
+            self.geom, self.geom_P = u8(lib.sb200_geom_bytes(cap)), cap
+        if self.image_WH != (W, H):
+            self.image, self.image_WH = u8(lib.sb200_image_bytes(W, H)), (W, H)
+
+    def fit_grad(self, P):
+        if P > self.grad_P:
+            cap = max(P, int(self.grad_P * 1.25))
+            self.grad_ws = torch.empty(_load().sb200_grad_bytes(cap), dtype=torch.uint8, device=self.device)
+            self.grad_P = cap
+
+    def grow_pairs(self, R):
+        lib = _load()
+        want = int(R * 1.25) + 4096
+        self.binning = torch.empty(lib.sb200_binning_bytes(want), dtype=torch.uint8, device=self.device)
+        self.point_list = torch.empty(want, dtype=torch.int32, device=self.device)
+        self.pair_capacity = want
 
 
-def _count_buffer(device):
-    key = device.index
-    buf = _pinned_counts.get(key)
-    if buf is None:
-        buf = torch.zeros(1, dtype=torch.int64).pin_memory()
-        _pinned_counts[key] = buf
-    return buf
+class _Lease:
+    """Ties a pooled workspace to the autograd node that needs it in its backward; the workspace returns to the pool
+    when the node dies (not at the first backward: retain_graph=True may run the backward again)."""
+
+    def __init__(self, ws):
+        self.ws = ws
+        ws.busy = True
+
+    def __del__(self):
+        self.ws.busy = False
+
+
+_pool = {}   # (device index, stream handle) -> [workspaces]
+
+
+def _acquire(device, P, W, H):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    lst = _pool.setdefault(key, [])
+    ws = next((w for w in lst if not w.busy), None)
+    if ws is None:
+        ws = _Workspace(device)
+        lst.append(ws)
+    ws.fit(P, W, H)
+    return _Lease(ws)
+
+
+def release_workspaces():
+    """Drop every pooled workspace that is not leased (frees their device memory)."""
+    for key in list(_pool):
+        _pool[key] = [w for w in _pool[key] if w.busy]
 
 
 STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam",
@@ -156,6 +233,17 @@ def profile_read():
     cnt = (ctypes.c_longlong * len(STAGES))()
     _check(_load().sb200_profile_read(ms, cnt), "sb200_profile_read")
     return {name: (ms[i], cnt[i]) for i, name in enumerate(STAGES)}
+
+
+_walk_cap_keepalive = None
+
+
+def debug_walk_cap(per_tile_cap):
+    """Test hook (include/surfel_b200.h, sb200_debug_walk_cap): int32/uint32 CUDA tensor [tiles] or None."""
+    global _walk_cap_keepalive
+    _walk_cap_keepalive = per_tile_cap
+    _check(_load().sb200_debug_walk_cap(_ptr(per_tile_cap) if per_tile_cap is not None else _vp(None)),
+           "sb200_debug_walk_cap")
 
 
 def launch_count():
@@ -221,31 +309,53 @@ class _RasterizeGaussians(torch.autograd.Function):
             return color, radii, others
 
         stream = _stream(dev)
-        geom = torch.empty(lib.sb200_geom_bytes(P), dtype=torch.uint8, device=dev)
-        image = torch.empty(lib.sb200_image_bytes(W, H), dtype=torch.uint8, device=dev)
-        count = _count_buffer(dev)
-        if ctx.use_pre:
-            _check(lib.sb200_forward_begin_precomp(P, W, H, _ptr(means3D), _ptr(tm_c), _ptr(opac), _ptr(colors),
-                                                   _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii),
-                                                   _vp(count.data_ptr()), stream), "sb200_forward_begin_precomp")
+        lease = _acquire(dev, P, W, H)
+        ws = lease.ws
+
+        def two_stage():
+            """Waits for the pair count after the preprocess, sizes the scratch, then bins and blends."""
+            if ctx.use_pre:
+                _check(lib.sb200_forward_begin_precomp(P, W, H, _ptr(means3D), _ptr(tm_c), _ptr(opac), _ptr(colors),
+                                                       _ptr(view), _ptr(proj), _ptr(ws.geom), _ptr(radii),
+                                                       _vp(ws.count.data_ptr()), stream), "sb200_forward_begin_precomp")
+            else:
+                _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac),
+                                               _ptr(colors), _ptr(view), _ptr(proj), _ptr(ws.geom), _ptr(radii),
+                                               _vp(ws.count.data_ptr()), stream), "sb200_forward_begin")
+            R = int(ws.count[0])
+            if R > ws.pair_capacity:
+                ws.grow_pairs(R)
+            _check(lib.sb200_forward_finish(P, W, H, R, _ptr(bg), _ptr(ws.geom), _vp(ws.binning.data_ptr()),
+                                            _vp(ws.point_list.data_ptr()), _ptr(ws.image), _ptr(color), _ptr(others),
+                                            stream), "sb200_forward_finish")
+            return R
+
+        if ctx.use_pre or ws.pair_capacity < 1:
+            R = two_stage()
         else:
-            _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac),
-                                           _ptr(colors), _ptr(view), _ptr(proj), _ptr(geom), _ptr(radii),
-                                           _vp(count.data_ptr()), stream), "sb200_forward_begin")
-        R = int(count[0])
+            # sync-free forward on the scratch kept from earlier calls: the whole forward is queued at once and the
+            # host only waits for the pair count (copied back right behind the preprocess) to confirm that the
+            # scratch was large enough -- the GPU never idles while the host sizes buffers
+            cap = ws.pair_capacity
+            _check(lib.sb200_forward_async(P, W, H, _ptr(means3D), _ptr(scales_c), _ptr(rot_c), _ptr(opac), _ptr(colors),
+                                           _ptr(view), _ptr(proj), _ptr(bg), _ptr(ws.geom), _ptr(radii),
+                                           _vp(ws.binning.data_ptr()), cap, _vp(ws.point_list.data_ptr()),
+                                           _ptr(ws.image), _ptr(color), _ptr(others), _vp(ws.count.data_ptr()),
+                                           _vp(ws.sync), stream), "sb200_forward_async")
+            _check(lib.sb200_forward_wait(_vp(ws.sync)), "sb200_forward_wait")
+            R = int(ws.count[0])
+            if R > cap:   # outgrown: only the first `cap` pairs were binned -- size up and run again
+                ws.grow_pairs(R)
+                R = two_stage()
         last_counters.update(P=P, R=R, W=W, H=H)
-        # sort scratch is dead after the forward; only the sorted id list is kept for the backward
-        binning = torch.empty(lib.sb200_binning_bytes(R), dtype=torch.uint8, device=dev)
-        point_list = torch.empty((R,), dtype=torch.int32, device=dev)
-        _check(lib.sb200_forward_finish(P, W, H, R, _ptr(bg), _ptr(geom), _ptr(binning), _ptr(point_list),
-                                        _ptr(image), _ptr(color), _ptr(others), stream), "sb200_forward_finish")
         ctx.empty = False
         ctx.raster_settings = rs
         ctx.P = P
         ctx.num_rendered = R
         ctx.sh_degree = int(rs.sh_degree)
-        ctx.save_for_backward(means3D, tm_c if ctx.use_pre else scales_c, rot_c, radii, geom, point_list, image, color,
-                              others, *((sh_c, clamped, campos) if ctx.use_sh else ()))
+        ctx.lease = lease   # geometry / image workspaces and the sorted id list live in the leased workspace
+        ctx.save_for_backward(means3D, tm_c if ctx.use_pre else scales_c, rot_c, radii, color, others,
+                              *((sh_c, clamped, campos) if ctx.use_sh else ()))
         ctx.mark_non_differentiable(radii)
         return color, radii, others
 
@@ -260,8 +370,10 @@ class _RasterizeGaussians(torch.autograd.Function):
             return tuple(torch.zeros(sh_, dtype=torch.float32, device=dev)
                          if sh_ is not None and ctx.needs_input_grad[i] else None
                          for i, sh_ in enumerate(ctx.in_shapes))
-        means3D, scales_c, rot_c, radii, geom, point_list, image, color, others = ctx.saved_tensors[:9]
+        means3D, scales_c, rot_c, radii, color, others = ctx.saved_tensors[:6]
         dev = means3D.device
+        ws = ctx.lease.ws
+        ws.fit_grad(P)
         g_color = _f32c(grad_out_color, "grad_out_color")
         g_others = _f32c(grad_depth, "grad_allmap")
         mask = rs.pixel_mask
@@ -277,11 +389,12 @@ class _RasterizeGaussians(torch.autograd.Function):
         proj = rs.projmatrix.contiguous()
         e = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         dmeans3D, dmeans2D, dcolors, dopac = e(P, 3), e(P, 3), e(P, 3), e(P, 1)
-        dscales, drot, dtrans, scores = e(P, 2), e(P, 4), e(P, 9), e(P, 2)
-        grad_ws = torch.empty(lib.sb200_grad_bytes(P), dtype=torch.uint8, device=dev)
-        tail = (_ptr(view), _ptr(proj), _ptr(radii), _ptr(geom), _ptr(point_list), _ptr(image), _ptr(color),
-                _ptr(others), _ptr(g_color), _ptr(g_others), _ptr(mask), _ptr(grad_ws), _ptr(dmeans3D), _ptr(dmeans2D),
-                _ptr(dcolors), _ptr(dopac), _ptr(dscales), _ptr(drot), _ptr(dtrans), _ptr(scores), _stream(dev))
+        dscales, drot, scores = e(P, 2), e(P, 4), e(P, 2)
+        dtrans = e(P, 9) if ctx.use_pre else None   # dL/dtransMat only exists for precomputed transforms
+        tail = (_ptr(view), _ptr(proj), _ptr(radii), _ptr(ws.geom), _vp(ws.point_list.data_ptr()), _ptr(ws.image),
+                _ptr(color), _ptr(others), _ptr(g_color), _ptr(g_others), _ptr(mask), _ptr(ws.grad_ws), _ptr(dmeans3D),
+                _ptr(dmeans2D), _ptr(dcolors), _ptr(dopac), _ptr(dscales), _ptr(drot), _ptr(dtrans), _ptr(scores),
+                _stream(dev))
         if ctx.use_pre:  # scales_c holds the precomputed transforms
             _check(lib.sb200_backward_precomp(P, W, H, ctx.num_rendered, _ptr(bg), float(rs.tanfovx),
                                               float(rs.tanfovy), _ptr(scales_c), *tail), "sb200_backward_precomp")
@@ -293,7 +406,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         dsh = None
         if ctx.use_sh:
             # dL/dcolors -> dL/dsh, plus the view-direction term of dL/dmeans3D (backward.cu:1038-1039)
-            sh_c, clamped, campos = ctx.saved_tensors[9:]
+            sh_c, clamped, campos = ctx.saved_tensors[6:]
             dsh = torch.empty_like(sh_c)
             _check(lib.sb200_sh_backward(P, ctx.sh_degree, sh_c.size(1), _ptr(means3D), _ptr(campos), _ptr(sh_c),
                                          _ptr(clamped), _ptr(radii), _ptr(dcolors), _ptr(dmeans3D), _ptr(dsh),

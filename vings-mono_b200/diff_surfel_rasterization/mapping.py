@@ -15,7 +15,7 @@ import ctypes
 
 import torch
 
-from . import _check, _count_buffer, _f32c, _load, _ptr, _stream, _vp, last_counters
+from . import _check, _f32c, _load, _ptr, _stream, _vp, last_counters
 
 UPDATE_LOCAL, UPDATE_DP_PRE, UPDATE_DP_POST = 0, 1, 2
 GROUP_COLS = (3, 3, 1, 2, 4)  # xyz, rgb, opacity, scaling, rotation
@@ -76,14 +76,29 @@ class RasterWorkspace:
         self.binning = u8(0)
         self.point_list = torch.empty(0, dtype=torch.int32, device=device)
         self.pair_capacity = 0   # pairs the binning scratch and point_list hold
-        self._pending = None     # (pinned count, capacity) of an unconfirmed forward_async
+        self._pending = None     # capacity of an unconfirmed forward_async
+        # hand-off state of the sync-free forward, owned by THIS workspace: a pinned landing pad for the pair count
+        # and the event recorded behind its copy (forwards of other workspaces / streams cannot disturb them)
+        self._count = torch.zeros(1, dtype=torch.int64).pin_memory()
+        self._sync = lib.sb200_sync_create()
+        if not self._sync:
+            raise RuntimeError("sb200_sync_create failed: %s" % lib.sb200_last_error().decode())
         self.color, self.allmap = f(3, H, W), f(7, H, W)
         self.loss_out = (f(7), f(3, H, W), f(7, H, W))
         self.pixel_mask = torch.ones(H * W, dtype=torch.bool, device=device)
         self.R = 0
+        self.R_seen = 0          # pair count of the last confirmed forward (diagnostics)
         self.capacity = 0
         self._alloc_rows(max(int(capacity or 0), P, 1))
         self.set_P(P)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_sync", None):
+                _load().sb200_sync_destroy(self._sync)
+                self._sync = None
+        except Exception:
+            pass
 
     def _alloc_rows(self, cap):
         """P-sized buffers for up to ``cap`` surfels (the layouts are monotone in P, so any P <= cap fits)."""
@@ -112,12 +127,12 @@ class RasterWorkspace:
         lib = _load()
         P, W, H, dev = self.P, self.W, self.H, self.device
         stream = _stream(dev)
-        count = _count_buffer(dev)
+        count = self._count
         _check(lib.sb200_forward_begin(P, W, H, _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(opacities),
                                        _ptr(colors), _ptr(viewmatrix), _ptr(projmatrix), _ptr(self.geom),
                                        _ptr(self.radii), _vp(count.data_ptr()), stream), "sb200_forward_begin")
         R = int(count[0])
-        self.R = R
+        self.R = self.R_seen = R
         last_counters.update(P=P, R=R, W=W, H=H)
         if R > self.pair_capacity:
             self._grow_pairs(R)
@@ -137,14 +152,14 @@ class RasterWorkspace:
         if cap < 1:
             self._pending = None
             return self.forward(means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix)
-        count = _count_buffer(dev)
         _check(lib.sb200_forward_async(P, W, H, _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(opacities),
                                        _ptr(colors), _ptr(viewmatrix), _ptr(projmatrix), _ptr(bg), _ptr(self.geom),
                                        _ptr(self.radii), _vp(self.binning.data_ptr()), cap,
                                        _vp(self.point_list.data_ptr()), _ptr(self.image), _ptr(self.color),
-                                       _ptr(self.allmap), _vp(count.data_ptr()), _stream(dev)), "sb200_forward_async")
+                                       _ptr(self.allmap), _vp(self._count.data_ptr()), _vp(self._sync), _stream(dev)),
+               "sb200_forward_async")
         self.R = cap  # what sb200_backward is told; the live count stays on the device
-        self._pending = (count, cap)
+        self._pending = cap
         return self.color, self.radii, self.allmap
 
     def confirm(self):
@@ -152,10 +167,11 @@ class RasterWorkspace:
         check it against the scratch capacity."""
         if self._pending is None:
             return True
-        count, cap = self._pending
+        cap = self._pending
         self._pending = None
-        _check(_load().sb200_forward_wait(), "sb200_forward_wait")
-        R = int(count[0])
+        _check(_load().sb200_forward_wait(_vp(self._sync)), "sb200_forward_wait")
+        R = int(self._count[0])
+        self.R_seen = R
         last_counters.update(P=self.P, R=R, W=self.W, H=self.H)
         if R <= cap:
             return True

@@ -134,7 +134,9 @@ def ply_to_scene(path, device="cpu"):
 def save_pt_ckpt(mapper, path):
     """gaussian_base.py:492-505: the five raw parameters and the score bookkeeping; like the reference, no optimizer
     state (load_pt_ckpt calls setup_optimizer(), i.e. Adam restarts from zero moments)."""
-    torch.save({k: getattr(mapper, k) for k in GROUPS + BOOK}, path)
+    # exact-size copies: in fused mode the attributes are [:P] views into the surfel store's capacity-sized buffers, and
+    # torch.save serialises a view's WHOLE storage (stale rows of pruned surfels included)
+    torch.save({k: getattr(mapper, k).detach().clone().contiguous() for k in GROUPS + BOOK}, path)
 
 
 def load_pt_ckpt(path, device=None):
