@@ -71,6 +71,12 @@ size_t sb200_geom_bytes(int64_t P);
 size_t sb200_image_bytes(int W, int H);
 /* sort scratch for R (tile,surfel) pairs (reference: BinningState, rasterizer_impl.h:86-97); dead after forward_finish */
 size_t sb200_binning_bytes(int64_t R);
+/* the pair list: u32 sorted surfel ids [R] followed by the forward's hit masks (one u32 per 32-surfel batch of a
+ * tile and warp of its CTA: which surfels of the batch some live pixel of the warp's 8x4 block may blend; the
+ * backward visits exactly those).  Written by sb200_forward_finish / _async, read by sb200_backward with the SAME
+ * R (or pair_capacity); must persist forward->backward.  Replaces the reference's per-bucket checkpoints
+ * (SampleState, rasterizer_impl.h:68-83: 13 KiB per 32 surfels) with ~1 byte per pair. */
+size_t sb200_pair_list_bytes(int64_t R, int W, int H);
 /* per-surfel gradient accumulation scratch for the backward: 80 B * P, zeroed by the library */
 size_t sb200_grad_bytes(int64_t P);
 /* byte offsets of the inspectable arrays inside the workspaces (tests / debugging):
@@ -98,14 +104,15 @@ int sb200_forward_begin(int P, int W, int H,
                         void* geom_ws, int* radii, int64_t* num_rendered_host, void* stream);
 
 /* Stage 2: pair emission in depth order, tile ranges, stable sort of the pairs by tile, per-tile blend.
- * point_list[R] (u32) receives the sorted surfel ids and must persist until the backward.
+ * point_list (sb200_pair_list_bytes(R, W, H) bytes) receives the sorted surfel ids [R] and, behind them, the hit
+ * masks; it must persist until the backward.
  * out_color [3,H,W]; out_others [7,H,W] = depth, alpha, normal xyz (view space), median depth, distortion. */
 int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg /* [3] */,
                          void* geom_ws, void* binning_ws, uint32_t* point_list, void* image_ws,
                          float* out_color, float* out_others, void* stream);
 
 /* Both stages in one call WITHOUT a host synchronisation, for callers that keep a binning scratch of
- * `pair_capacity` pairs (sb200_binning_bytes(pair_capacity), point_list[pair_capacity]): every launch takes the
+ * `pair_capacity` pairs (sb200_binning_bytes(pair_capacity), sb200_pair_list_bytes(pair_capacity, W, H)): every launch takes the
  * pair count from device memory.  R is copied to *num_rendered_host (pinned host memory, owned by the caller's
  * workspace) right after the preprocess and `sync` (a handle from sb200_sync_create, one per workspace) is recorded
  * behind that copy; sb200_forward_wait(sync) blocks until the copy has landed - call it wherever convenient before
@@ -194,6 +201,36 @@ int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp
                         int64_t* kf_id, int64_t kf, float* fused, const float* lr, float b1, float b2, float eps,
                         void* stream);
 
+/* ---- multi-GPU exchange of the mapping step over NVLink peer memory ----------------------
+ * One optimizer step takes ONE view per rank (window views partitioned over the GPUs of a box, surfels replicated).
+ * The three calls below replace "sb200_surfel_update(DP_PRE) -> NCCL all-reduce of [16,P] -> sb200_surfel_update(
+ * DP_POST)" by kernels that read their peers' buffers directly; the caller provides peer-mapped allocations (one
+ * pointer per rank to the same buffer of that rank, e.g. torch symmetric memory) and a barrier over the ranks between
+ * the calls (all three are stream ordered).  Surfel i is owned by rank i / slice.
+ *   sb200_dp_stage : backward of the activations; for a visible surfel (radii > 0) writes its 13 raw-parameter
+ *                    gradients and two scores to stage[i] (16 floats), vis[i] = radii > 0.  Local buffers of the rank
+ *                    (sb200_dp_stage_bytes(P) bytes, P bytes).
+ *   sb200_dp_reduce: for the owned surfels lo <= i < hi: loads the stage rows of every rank q with peer_vis[q][i],
+ *                    applies weighting_grad per view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views in
+ *                    rank order: gradient sum, score-0 sum, score-1 max, first arg-max of score 0 with its keyframe id
+ *                    kf_ids[q] (HOST array, one id per rank) -> out[i - lo] (20 floats), upd[i - lo] = seen by any view.
+ *   sb200_dp_post  : every rank, every surfel: loads the owner's result row (peer_out / peer_upd), applies add_records
+ *                    (scripts/gaussian/gaussian_model.py:163-168) for the folded views and the masked Adam step
+ *                    (cuda_rasterizer/adam.cu:9-38) to the local replica.  All ranks read the same bytes: the replicas
+ *                    stay bit-identical, and equal a single process that takes the same views in rank order.
+ * params / exp_avg / exp_avg_sq / lr: as sb200_surfel_update.  peer_*: HOST arrays of n_ranks (<= 16) device pointers. */
+size_t sb200_dp_stage_bytes(int64_t P);
+size_t sb200_dp_out_bytes(int64_t slice);
+int sb200_dp_stage(int P, const float* d_means3D, const float* d_colors, const float* d_opacity, const float* d_scales,
+                   const float* d_rotations, const float* cur_scores, const int* radii, const float* opacity_raw,
+                   const float* scaling_raw, const float* rotation_raw, float* stage, uint8_t* vis, void* stream);
+int sb200_dp_reduce(int lo, int hi, int n_ranks, const void* const* peer_stage, const void* const* peer_vis,
+                    const int64_t* kf_ids, const float* global_scores, float* out, uint8_t* upd, void* stream);
+int sb200_dp_post(int P, int slice, int n_ranks, const void* const* peer_out, const void* const* peer_upd,
+                  float* const* params, float* const* exp_avg, float* const* exp_avg_sq, const uint8_t* stable_mask,
+                  float* local_scores, float* global_scores, float* kf_max_scores, int64_t* kf_id, const float* lr,
+                  float b1, float b2, float eps, void* stream);
+
 /* ---- surfel add / prune churn --------------------------------------------
  * sb200_knn_mean_dist2: out[i] = mean of the squared distances from points[i] to its 3 nearest OTHER points, i.e.
  * (KDTree(points).query(points, k=4)[0][:, 1:] ** 2).mean(1) of the reference's distCUDA2
@@ -256,7 +293,7 @@ int sb200_sort_pairs(void* binning_ws, int64_t n, int end_bit, int mode, uint32_
 /* Test hook for reference quirk Q17: the reference's forward stores a per-tile `max_contrib`
  * (cuda_rasterizer/forward.cu:496-502) that its backward uses to drop whole 32-surfel buckets (backward.cu:503-505),
  * and that value is not the tile maximum (cub::BlockReduce<.,256> on a 16x16 block).  With per_tile_cap (device
- * u32[tiles], must stay alive) set, the calling thread's following sb200_backward calls stop every tile's walk at
+ * u32[tiles], must stay alive) set, the process's following sb200_backward calls stop every tile's walk at
  * ceil(cap/32) buckets exactly like the reference does, which lets a test show that this quirk explains ALL of the
  * gradient difference on the surfels it excludes.  NULL switches it off (the default). */
 int sb200_debug_walk_cap(const uint32_t* per_tile_cap);

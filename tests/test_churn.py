@@ -103,9 +103,10 @@ LOSS_TOL = 2e-5   # relative; measured ~1e-6 (fp32 summation order of the SSIM f
 def _train_both(a, b, scene, v, step, dev):
     gt = {k: t.cuda() for k, t in synthetic.make_gt(scene, v, step).items()}
     vd = mapper_step.view_to_device(v, dev)
+    before = util.mapper_snapshot(b)
     la, lb = float(a.train_view(vd, gt, kf_id=step + 1)), float(b.train_view(vd, gt, kf_id=step + 1))
     assert np.isfinite(lb) and abs(la - lb) <= LOSS_TOL * max(1.0, abs(la)), (step, la, lb)
-    util.assert_one_step_agrees(a, b, ctx="step %d" % step)
+    util.assert_one_step_agrees(a, b, before, ctx="step %d" % step)
     util.sync_mapper_state(a, b)
 
 

@@ -13,6 +13,9 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "vings-mono_b200"), os.path.join(ROOT, "tests")]
 
 
+BOOK = ("_local_scores", "_globalkf_max_scores", "_globalkf_id")
+
+
 def _setup():
     import emu_module
     import mapper_step
@@ -28,12 +31,17 @@ def _worker(rank, port, out):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=2)
     mod, ms, scene, vds, gts = _setup()
-    mapper = ms.SurfelMapper(mod, scene, torch.device("cpu"), "rgb+depth", world_size=2, process_group=dist.group.WORLD)
+    mapper = ms.SurfelMapper(mod, scene, torch.device("cpu"), "rgb+depth", world_size=2, process_group=dist.group.WORLD,
+                             rank=rank)
     for it in range(2):
+        ids = [(it + q) % 2 + 10 * it for q in range(2)]       # keyframe ids of both ranks' views, rank order
         v = (it + rank) % 2
-        loss = mapper.train_view(vds[v], gts[v], kf_id=v)
+        # step 0 passes the schedule, step 1 lets the mapper gather it (all_gather_object)
+        loss = mapper.train_view(vds[v], gts[v], kf_id=ids[rank], kf_ids=ids if it == 0 else None)
     res = {k: getattr(mapper, k).detach().clone() for k in ms.GROUPS}
     res["scores"] = mapper._global_scores.clone()
+    for k in BOOK:
+        res[k] = getattr(mapper, k).clone()
     res["fused"] = mapper._fused.clone()
     res["loss"] = float(loss)
     out[rank] = res
@@ -48,7 +56,8 @@ def test_two_rank_step_equals_single_process_batched_step():
     a, b = out[0], out[1]
     mod, ms, scene, vds, gts = _setup()
     # replicas stay bit-identical (the all-reduce returns the same bits everywhere, Adam is deterministic)
-    for k in list(ms.GROUPS) + ["scores"]:
+    # -- the whole score bookkeeping included: add_records is applied for every view in rank order on every rank
+    for k in list(ms.GROUPS) + ["scores"] + list(BOOK):
         assert torch.equal(a[k], b[k]), k
     # single-process restatement of the batched step: per-view weighting, summed grads/scores, OR-ed visibility
     ref = ms.SurfelMapper(mod, scene, torch.device("cpu"), "rgb+depth")
@@ -56,19 +65,20 @@ def test_two_rank_step_equals_single_process_batched_step():
         grads = {k: torch.zeros_like(getattr(ref, k)) for k in ms.GROUPS}
         score_sum = torch.zeros(ref.P, 2)
         vis = torch.zeros(ref.P, dtype=torch.bool)
+        g0 = ref._global_scores[:, 0].clone()   # every view of a step is weighted with the scores from BEFORE the step
         for r in range(2):
             v = (it + r) % 2
             pred = ref.render(vds[v])
             ms.get_loss(ref.weights, pred, gts[v], ref.window).backward()
             cur = ref._zeros.grad.detach()
-            gw = (cur[:, 0] / (torch.clamp(ref._global_scores[:, 0] + cur[:, 0], 0, 1e4) + 1e-6 + cur[:, 0])).unsqueeze(1)
+            gw = (cur[:, 0] / (torch.clamp(g0 + cur[:, 0], 0, 1e4) + 1e-6 + cur[:, 0])).unsqueeze(1)
             for k in ms.GROUPS:
                 grads[k] += getattr(ref, k).grad * gw
                 getattr(ref, k).grad = None
             score_sum += cur
             vis |= pred["radii"] > 0
+            ref._add_records(cur, (it + r) % 2 + 10 * it)    # view by view, in rank order
         last_grads = torch.cat([grads[k].reshape(-1) for k in ms.GROUPS])
-        ref._add_records(score_sum, 0)
         for k in ms.GROUPS:
             getattr(ref, k).grad = grads[k]
         ref.optimizer.step(vis, ref.P)
@@ -85,6 +95,10 @@ def test_two_rank_step_equals_single_process_batched_step():
         assert float(close.float().mean()) > 0.98, (k, float(close.float().mean()))
         assert float((a[k] - getattr(ref, k).detach()).abs().max()) <= 2 * 2 * 3.2 * ms.LR[k] + 1e-6, k
     assert torch.allclose(a["scores"], ref._global_scores, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(a["_local_scores"], ref._local_scores, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(a["_globalkf_max_scores"], ref._globalkf_max_scores, rtol=1e-5, atol=1e-7)
+    assert float((a["_globalkf_id"] != ref._globalkf_id).float().mean()) < 0.02   # ties broken by ulp-level score noise
+    assert int(a["_globalkf_id"].max()) >= 10                                     # ids of the second step were recorded
     # and something was actually learned/moved
     assert float((a["_opacity"] - torch.logit(scene["opacities"].clamp(1e-6, 1 - 1e-6))).abs().max()) > 0
 

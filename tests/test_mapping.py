@@ -176,9 +176,10 @@ def test_fused_view_matches_torch_view(sup):
         v = views[-1 - (i % len(views))]
         gt = {k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()}
         vd = mapper_step.view_to_device(v, dev)
+        before = util.mapper_snapshot(b)
         la, lb = float(a.train_view(vd, gt, kf_id=i + 1)), float(b.train_view(vd, gt, kf_id=i + 1))
         assert abs(la - lb) <= 2e-5 * max(1.0, abs(la)), (i, la, lb)
-        util.assert_one_step_agrees(a, b, ctx="%s view %d" % (sup, i))
+        util.assert_one_step_agrees(a, b, before, ctx="%s view %d" % (sup, i))
         util.sync_mapper_state(a, b)
     for k in mapper_step.GROUPS:
         assert float((getattr(b, k).data - init[k]).abs().sum()) > 0, k
@@ -242,14 +243,14 @@ def test_forward_async_is_the_forward_and_survives_a_too_small_scratch():
     io = (ctypes.c_size_t * 3)()
     mine._load().sb200_image_layout(inp["W"], inp["H"], io)
     kept = io[2] + 8 * inp["W"] * inp["H"]   # ranges, final T/M1/M2, contributor counts (the launch order is not unique)
-    ref = (a.color.clone(), a.allmap.clone(), a.radii.clone(), a.point_list[:R].clone(), a.image[:kept].clone())
+    ref = (a.color.clone(), a.allmap.clone(), a.radii.clone(), a.sorted_ids(R).clone(), a.image[:kept].clone())
     assert R > 5000
     # same workspace again, asynchronously (scratch holds 1.25 R pairs)
     a.color.zero_(); a.allmap.zero_(); a.point_list.zero_()
     a.forward_async(*args)
     assert a.confirm() and mp.last_counters["R"] == R
     torch.cuda.synchronize()
-    got = (a.color, a.allmap, a.radii, a.point_list[:R], a.image[:kept])
+    got = (a.color, a.allmap, a.radii, a.sorted_ids(R), a.image[:kept])
     for x, y in zip(got, ref):
         assert torch.equal(x, y)
     # a scratch of R/3 pairs surrounded by canaries: nothing outside is written, confirm() says no and grows it
@@ -258,14 +259,125 @@ def test_forward_async_is_the_forward_and_survives_a_too_small_scratch():
     nbytes = mine._load().sb200_binning_bytes(small)
     guard = 4096
     bin_buf = torch.full((nbytes + 2 * guard,), 0x5A, dtype=torch.uint8, device=dev)
-    pl_buf = torch.full((small + 2 * guard,), 0x5A5A5A5A, dtype=torch.int32, device=dev)
-    b.binning, b.point_list, b.pair_capacity = bin_buf[guard:guard + nbytes], pl_buf[guard:guard + small], small
+    pl_bytes = mine._load().sb200_pair_list_bytes(small, inp["W"], inp["H"])
+    pl_buf = torch.full((pl_bytes + 2 * guard,), 0x5A, dtype=torch.uint8, device=dev)
+    b.binning, b.point_list, b.pair_capacity = bin_buf[guard:guard + nbytes], pl_buf[guard:guard + pl_bytes], small
     b.forward_async(*args)
     torch.cuda.synchronize()
     assert (bin_buf[:guard] == 0x5A).all() and (bin_buf[guard + nbytes:] == 0x5A).all()
-    assert (pl_buf[:guard] == 0x5A5A5A5A).all() and (pl_buf[guard + small:] == 0x5A5A5A5A).all()
+    assert (pl_buf[:guard] == 0x5A).all() and (pl_buf[guard + pl_bytes:] == 0x5A).all()
     assert not b.confirm() and b.pair_capacity >= R
     b.forward(*args)
     torch.cuda.synchronize()
-    for x, y in zip((b.color, b.allmap, b.radii, b.point_list[:R]), ref):
+    for x, y in zip((b.color, b.allmap, b.radii, b.sorted_ids(R)), ref):
         assert torch.equal(x, y)
+
+
+@pytest.mark.gpu
+def test_peer_exchange_kernels_equal_the_batched_step_on_one_device():
+    """The three kernels of the NVLink exchange (sb200_dp_stage / _reduce / _post, csrc/dp_exchange.cu) with the
+    "ranks" emulated on ONE device (every rank's buffers are ordinary tensors here, the peer pointer arrays point at
+    them): the result must be, bit for bit, (a) what the NCCL formulation gives when its two all-reduces are replaced
+    by torch sums / maxima over the same per-view rows, and (b) for the score bookkeeping, what add_records
+    (gaussian_model.py:163-168) gives when applied view by view in rank order."""
+    mine = util.load_mine()
+    mp, lib = mine.mapping, mine._load()
+    N = 3
+    scene, views = synthetic.make_scene("C3", P=30000, W=160, H=96)
+    dev = torch.device("cuda")
+    sup = "rgb+depth+normal+dist"
+    m = mapper_step.SurfelMapper(mine, scene, dev, supervision=sup, fused=True)
+    gts = [{k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()} for i, v in enumerate(views[:N + 1])]
+    vds = [mapper_step.view_to_device(v, dev) for v in views[:N + 1]]
+    m.train_view(vds[N], gts[N], kf_id=9)            # non-trivial moments and scores
+    P = m.P
+    g = torch.Generator(device="cpu").manual_seed(4)
+    stable = (torch.rand(P, generator=g) < 0.1).cuda()
+    prm = [getattr(m, k).data for k in mapper_step.GROUPS]
+    lr = [mapper_step.LR[k] for k in mapper_step.GROUPS]
+    kf_ids = [5, 3, 8]
+    # one backward per "rank" from the same parameters, each into its own workspace
+    wss = []
+    opac, scales, rot = mp.activate(prm[2], prm[3], prm[4])
+    for q in range(N):
+        ws = mp.RasterWorkspace(P, m.W, m.H, dev)
+        ws.forward(prm[0], scales, rot, opac, prm[1], m.bg, vds[q]["viewmatrix"], vds[q]["projmatrix"])
+        loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gts[q]["rgb"], gts[q]["depth"], gts[q]["depth_cov"],
+                                              vds[q]["w2c"], m.cx, m.cy, m.fx, m.fy, m.weights, ws=ws.loss_ws, out=ws.loss_out)
+        ws.backward(d_color, d_allmap, prm[0], scales, rot, m.bg, vds[q]["viewmatrix"], vds[q]["projmatrix"],
+                    vds[q]["tanfovx"], vds[q]["tanfovy"])
+        wss.append(ws)
+    assert sum(int((ws.radii > 0).sum()) for ws in wss) > P // 2
+
+    def state():
+        st = [m.optimizer.state[getattr(m, k)] for k in mapper_step.GROUPS]
+        return ([p.clone() for p in prm], [x["exp_avg"].clone() for x in st], [x["exp_avg_sq"].clone() for x in st],
+                [m._local_scores.clone(), m._global_scores.clone(), m._globalkf_max_scores.clone(), m._globalkf_id.clone()])
+
+    # ---- (A) the peer-memory kernels, ranks emulated ----
+    pa, ma, va, ba = state()
+    vp = ctypes.c_void_p
+    st_ = vp(torch.cuda.current_stream().cuda_stream)
+    S = ((P + N - 1) // N + 255) // 256 * 256
+    stage = [torch.full((lib.sb200_dp_stage_bytes(P) // 4,), float("nan"), device=dev) for _ in range(N)]
+    vis = [torch.full((P,), 7, dtype=torch.uint8, device=dev) for _ in range(N)]
+    out = [torch.full((lib.sb200_dp_out_bytes(S) // 4,), float("nan"), device=dev) for _ in range(N)]
+    upd = [torch.full((S,), 7, dtype=torch.uint8, device=dev) for _ in range(N)]
+    parr = lambda ts: (vp * N)(*[t.data_ptr() for t in ts])
+    for q in range(N):
+        ws = wss[q]
+        assert lib.sb200_dp_stage(P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()), vp(ws.d_opacity.data_ptr()),
+                                  vp(ws.d_scales.data_ptr()), vp(ws.d_rot.data_ptr()), vp(ws.scores.data_ptr()),
+                                  vp(ws.radii.data_ptr()), vp(prm[2].data_ptr()), vp(prm[3].data_ptr()),
+                                  vp(prm[4].data_ptr()), vp(stage[q].data_ptr()), vp(vis[q].data_ptr()), st_) == 0
+    kf_arr = (ctypes.c_int64 * N)(*kf_ids)
+    for r in range(N):
+        lo, hi = min(P, r * S), min(P, (r + 1) * S)
+        assert lib.sb200_dp_reduce(lo, hi, N, parr(stage), parr(vis), kf_arr, vp(ba[1].data_ptr()),
+                                   vp(out[r].data_ptr()), vp(upd[r].data_ptr()), st_) == 0, lib.sb200_last_error()
+    arr5 = lambda ts: (vp * 5)(*[t.data_ptr() for t in ts])
+    assert lib.sb200_dp_post(P, S, N, parr(out), parr(upd), arr5(pa), arr5(ma), arr5(va), vp(stable.data_ptr()),
+                             vp(ba[0].data_ptr()), vp(ba[1].data_ptr()), vp(ba[2].data_ptr()), vp(ba[3].data_ptr()),
+                             (ctypes.c_float * 5)(*lr), 0.9, 0.999, 1e-15, st_) == 0, lib.sb200_last_error()
+    torch.cuda.synchronize()
+
+    # ---- (B) the NCCL formulation with the collectives replaced by torch reductions over the same rows ----
+    pb, mb, vb, bb = state()
+    fused = torch.zeros(16 * P, device=dev)
+    s1_max = torch.zeros(P, device=dev)
+    s0_max = torch.full((P,), -1.0, device=dev)
+    kf_arg = torch.zeros(P, dtype=torch.int64, device=dev)
+    for q in range(N):
+        f = torch.zeros(16 * P, device=dev)
+        mp.surfel_update(mp.UPDATE_DP_PRE, pb, mb, vb, lr, wss[q], stable, *bb, kf_ids[q], fused=f)
+        fused += f
+        cur = wss[q].scores
+        s1_max = torch.maximum(s1_max, cur[:, 1])
+        first = (cur[:, 0] > s0_max) & (wss[q].radii > 0)
+        s0_max = torch.where(first, cur[:, 0], s0_max)
+        kf_arg = torch.where(first, torch.full_like(kf_arg, kf_ids[q]), kf_arg)
+    fused[13 * P:15 * P].view(P, 2)[:, 1] = s1_max
+    kfm0, kid0 = bb[2].clone(), bb[3].clone()
+    mp.surfel_update(mp.UPDATE_DP_POST, pb, mb, vb, lr, wss[0], stable, *bb, kf_ids[0], fused=fused)
+    replace = kfm0 < s0_max
+    bb[2].copy_(torch.where(replace, s0_max, kfm0))
+    bb[3].copy_(torch.where(replace, kf_arg, kid0))
+    names = ["p%d" % i for i in range(5)] + ["m%d" % i for i in range(5)] + ["v%d" % i for i in range(5)] + \
+            ["local", "global", "kf_max", "kf_id"]
+    for n_, x, y in zip(names, pa + ma + va + ba, pb + mb + vb + bb):
+        assert torch.equal(x, y), (n_, float((x.double() - y.double()).abs().max()))
+    assert not torch.equal(pa[0], prm[0]) and torch.equal(pa[0][stable], prm[0][stable])
+
+    # ---- (C) add_records view by view, in rank order ----
+    loc, glo, kfm, kid = m._local_scores.clone(), m._global_scores.clone(), m._globalkf_max_scores.clone(), m._globalkf_id.clone()
+    for q in range(N):
+        cur = wss[q].scores
+        loc[:, 0] += cur[:, 0]
+        loc[:, 1] = torch.where(cur[:, 1] > loc[:, 1], cur[:, 1], loc[:, 1])
+        glo[:, 0] += cur[:, 0]
+        glo = torch.clamp(glo, 0, 1e4)
+        rep = kfm < cur[:, 0]
+        kfm = torch.where(rep, cur[:, 0], kfm)
+        kid = torch.where(rep, torch.full_like(kid, kf_ids[q]), kid)
+    assert torch.equal(ba[2], kfm) and torch.equal(ba[3], kid) and torch.equal(ba[0][:, 1], loc[:, 1])
+    assert torch.allclose(ba[0][:, 0], loc[:, 0], rtol=1e-6, atol=0) and torch.allclose(ba[1], glo, rtol=1e-6, atol=0)

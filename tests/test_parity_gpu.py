@@ -24,7 +24,7 @@ pytestmark = pytest.mark.gpu
 # this implementation reduces 32 pixels by shuffle, 8 warps through shared memory and tiles by atomics -- a
 # different, also nondeterministic, association.  Measured agreement: 5e-7 (C1) .. 7e-5 (C2) relative L1.
 GRAD_TOL = 5e-4
-TAINT_BOUND = 0.10   # share of the visible surfels quirk Q17 may exclude (measured 0 .. 4 %)
+TAINT_TILES = 0.15   # share of the tiles whose stored max_contrib quirk Q17 may corrupt (measured 0 .. 7 %)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
@@ -93,14 +93,14 @@ def test_gradients_match_reference(mine, ref, name, kw):
     gen = torch.Generator(device="cpu").manual_seed(5)
     mask = (torch.rand(inp["W"] * inp["H"], generator=gen) < 0.8).cuda()   # exercises pixel_mask (Q14)
     om = util.run_impl(mine, inp, gc, ga, mask)
-    orf = util.run_impl(ref, inp, gc, ga, mask)
-    ri = util.ref_intermediates(ref, inp)
-    ids, nbad = util.tainted_surfels(ri, inp["W"], inp["H"])   # reference UB, quirk Q17
+    orf = util.run_impl(ref, inp, gc, ga, mask, ref_state=True)
+    # reference UB, quirk Q17: read off the buffers of the same forward whose backward produced orf's gradients
+    ids, nbad = util.tainted_surfels(orf["state"], inp["W"], inp["H"])
     keep = torch.ones(om["d_scores"].shape[0], dtype=torch.bool)
     keep[torch.from_numpy(ids)] = False
     # the exclusion set (reference UB, Q17) is bounded; test_parity_full_gpu.py proves it is exactly right
-    V = int((orf["radii"] > 0).sum())
-    assert len(ids) <= TAINT_BOUND * max(V, 1), (len(ids), V, nbad)
+    tiles_n = ((inp["W"] + 15) // 16) * ((inp["H"] + 15) // 16)
+    assert nbad <= TAINT_TILES * tiles_n, (nbad, tiles_n, len(ids))
     assert torch.equal(om["radii"], orf["radii"])
     for k in ("d_means3D", "d_means2D", "d_colors", "d_opacities", "d_scales", "d_rotations", "d_scores"):
         assert om[k].shape == orf[k].shape
@@ -117,9 +117,8 @@ def test_scores_with_zero_upstream_gradient(mine, ref):
     """Q13: scripts/loop/loop_model.py:180-186 backpropagates a zero loss only to read scores[:,0]."""
     inp, gc, ga = _case("C1", P=3000)
     om = util.run_impl(mine, inp, torch.zeros_like(gc), torch.zeros_like(ga))
-    orf = util.run_impl(ref, inp, torch.zeros_like(gc), torch.zeros_like(ga))
-    ri = util.ref_intermediates(ref, inp)
-    ids, _ = util.tainted_surfels(ri, inp["W"], inp["H"])
+    orf = util.run_impl(ref, inp, torch.zeros_like(gc), torch.zeros_like(ga), ref_state=True)
+    ids, _ = util.tainted_surfels(orf["state"], inp["W"], inp["H"])
     keep = torch.ones(om["d_scores"].shape[0], dtype=torch.bool)
     keep[torch.from_numpy(ids)] = False
     assert float(om["d_scores"][:, 0].sum()) > 0

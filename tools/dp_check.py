@@ -1,0 +1,126 @@
+"""Multi-rank parity of the fused mapping step on real GPUs (run under torchrun, one rank per GPU):
+
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port P tools/dp_check.py
+
+Every rank trains the same seeded map for a few optimizer steps, each step on its own view of the window, through
+(a) the peer-memory exchange (csrc/dp_exchange.cu) and (b) the NCCL formulation, and checks:
+  1. after every path the replicas are BIT-IDENTICAL on all ranks: parameters, Adam moments, and the whole score
+     bookkeeping (_local_scores, _global_scores, _globalkf_max_scores, _globalkf_id);
+  2. the two exchanges agree: bit for bit at 2 ranks (a two-term sum has one order), to fp32 summation order above
+     (NCCL's ring order is not the rank order);
+  3. rank 0: the step count, surfels updated, and that a prune + densify in between keeps the ranks in lockstep.
+Prints one JSON line on rank 0; exit code 1 on any mismatch."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "vings-mono_b200")]
+import torch
+import torch.distributed as dist
+
+import mapper_step
+import synthetic
+
+BOOK = ("_local_scores", "_global_scores", "_globalkf_max_scores", "_globalkf_id", "_stable_mask")
+
+
+def state_of(m):
+    out = {}
+    for k in mapper_step.GROUPS:
+        p = getattr(m, k)
+        st = m.optimizer.state[p]
+        out[k] = p.data.clone()
+        out["m" + k] = st["exp_avg"].clone()
+        out["v" + k] = st["exp_avg_sq"].clone()
+    for k in BOOK:
+        out[k] = getattr(m, k).clone()
+    return out
+
+
+def checksum(t):
+    """Order-independent but bit-sensitive: the wrapped int64 sum of the 32-bit words, and of words times index."""
+    w = t.contiguous().view(torch.uint8).reshape(-1)
+    pad = (-w.numel()) % 4
+    if pad:
+        w = torch.cat([w, w.new_zeros(pad)])
+    w = w.view(torch.int32).to(torch.int64)
+    idx = torch.arange(w.numel(), device=w.device, dtype=torch.int64) % 65521 + 1
+    return torch.stack([w.sum(), (w * idx).sum()])
+
+
+def run(mod, scene, views, gts, vds, dev, rank, world, exchange, steps, churn):
+    m = mapper_step.SurfelMapper(mod, scene, dev, supervision="rgb+depth+normal+dist", world_size=world,
+                                 process_group=dist.group.WORLD, fused=True, rank=rank, exchange=exchange)
+    K = len(views)
+    g = torch.Generator(device="cpu").manual_seed(3)
+    for it in range(steps):
+        ids = [(it * world + q) % K for q in range(world)]
+        m.train_view(vds[ids[rank]], gts[ids[rank]], kf_id=ids[rank], kf_ids=ids)
+        if churn and it == steps // 2:
+            mask = (torch.rand(m.P, generator=g) < 0.05).to(dev)       # same seeded mask on every rank
+            m.prune(mask)
+            n_new = 2000
+            xyz = (scene["means3D"][:n_new] + 0.01 * torch.randn(n_new, 3, generator=g)).to(dev)
+            m.add_surfels(xyz, torch.rand(n_new, 3, generator=g).to(dev), torch.randn(n_new, 4, generator=g).to(dev))
+    torch.cuda.synchronize()
+    return m, state_of(m)
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ.get("LOCAL_RANK", rank))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    import diff_surfel_rasterization as mod
+    mod._load()
+    P = int(os.environ.get("DP_CHECK_P", "60000"))
+    scene, views = synthetic.make_scene("C3", P=P, K=8, W=320, H=192)
+    gts = [{k: t.to(dev) for k, t in synthetic.make_gt(scene, v, i).items()} for i, v in enumerate(views)]
+    vds = [mapper_step.view_to_device(v, dev) for v in views]
+    steps = 6
+    ok, report = True, {"world": world, "P": P, "steps": steps}
+    states = {}
+    for exchange in ("p2p", "nccl"):
+        m, st = run(mod, scene, views, gts, vds, dev, rank, world, exchange, steps, churn=True)
+        report[exchange + "_used"] = m.exchange
+        states[exchange] = st
+        # 1. replicas bit-identical
+        sums = torch.stack([checksum(t) for t in st.values()])
+        allsums = [torch.empty_like(sums) for _ in range(world)]
+        dist.all_gather(allsums, sums)
+        same = all(torch.equal(allsums[0], s) for s in allsums)
+        report[exchange + "_replicas_identical"] = bool(same)
+        report[exchange + "_P_final"] = m.P
+        ok &= same
+        del m
+    # 2. the two exchanges agree
+    worst = 0.0
+    for k in states["p2p"]:
+        a, b = states["p2p"][k], states["nccl"][k]
+        if world == 2 or not a.dtype.is_floating_point:
+            eq = torch.equal(a, b) if k != "_globalkf_id" or world == 2 else float((a != b).float().mean()) < 1e-3
+            if not eq:
+                ok = False
+                report.setdefault("mismatch", []).append(k)
+        else:
+            rel = float((a.double() - b.double()).abs().sum() / b.double().abs().sum().clamp(min=1e-30))
+            worst = max(worst, rel)
+            if rel > 2e-3:   # Adam turns summation-order noise into sign-like flips on a few elements (see tests/util.py)
+                ok = False
+                report.setdefault("mismatch", []).append((k, rel))
+    report["p2p_vs_nccl_worst_rel"] = worst
+    moved = float((states["p2p"]["_xyz"][:1000] != scene["means3D"][:1000].to(dev)).float().mean())
+    report["moved_frac_first_1000"] = moved
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    report["ok"] = bool(int(flag[0]))
+    if rank == 0:
+        print(json.dumps(report), flush=True)
+    dist.destroy_process_group()
+    return 0 if report["ok"] else 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())

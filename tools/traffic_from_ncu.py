@@ -2,12 +2,25 @@
 per stage, the measured DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) and executed warp instructions
 (smsp__inst_executed.sum) summed over the stage's launches.  bench.py reads the file for roofline.traffic / .issue.
 
-Usage: python tools/traffic_from_ncu.py REPORT.ncu-rep C2 > profiles/traffic.json"""
+Usage: python tools/traffic_from_ncu.py REPORT.ncu-rep C2 [CSRC_HASH] > profiles/traffic.json"""
 import csv
+import importlib.util
 import io
 import json
+import os
 import subprocess
 import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _stamp():
+    """git SHA of HEAD and the content hash of csrc/ at capture-summary time (the capture must be of this build)."""
+    spec = importlib.util.spec_from_file_location("sb200_build", os.path.join(ROOT, "vings-mono_b200", "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    sha = subprocess.run(["git", "-C", ROOT, "rev-parse", "HEAD"], capture_output=True, text=True).stdout.strip()
+    return sha, mod.csrc_hash()
 
 # kernel name prefix -> stage (the names of include/surfel_b200.h's stage enum as bench.py spells them)
 STAGE_OF = [
@@ -37,7 +50,11 @@ def main():
         val = {n: float(r[i]) * UNIT.get(units[i], 1.0) for n, i in cols.items()}
         traffic[stage] = traffic.get(stage, 0.0) + val["dram__bytes_read.sum"] + val["dram__bytes_write.sum"]
         inst[stage] = inst.get(stage, 0.0) + val["smsp__inst_executed.sum"]
-    out = {"_source": "%s: one ncu --set full capture of every kernel of one %s mapping view (dram__bytes_read.sum + "
+    sha, chash = _stamp()
+    if len(sys.argv) > 3:   # the hash the capture was made with (written next to the report on the GPU box)
+        chash = sys.argv[3]
+    out = {"_git_sha": sha, "_csrc_hash": chash,
+           "_source": "%s: one ncu --set full capture of every kernel of one %s mapping view (dram__bytes_read.sum + "
                       "dram__bytes_write.sum and smsp__inst_executed.sum, summed over the launches of a stage); "
                       "made by tools/traffic_from_ncu.py" % (rep, cfg),
            cfg: traffic, cfg + "_warp_inst": inst}

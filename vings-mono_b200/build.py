@@ -16,9 +16,22 @@ VARIANT = os.environ.get("SB200_VARIANT", "")
 OBJ = OBJ + ("_" + VARIANT if VARIANT else "")
 OUT = os.path.join(HERE, "diff_surfel_rasterization", "libsurfel_b200%s.so" % ("_" + VARIANT if VARIANT else ""))
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "radix_sort.cu", "blend_forward.cu", "blend_backward.cu",
-           "preprocess_backward.cu", "map_loss.cu", "surfel_update.cu", "churn.cu", "sh_color.cu"]
+           "preprocess_backward.cu", "map_loss.cu", "surfel_update.cu", "dp_exchange.cu", "churn.cu", "sh_color.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xptxas", "-v"] + os.environ.get("SB200_EXTRA_FLAGS", "").split()
+
+
+def csrc_hash():
+    """sha1 over the kernel sources and the ABI header: stamps profiles/traffic.json (tools/traffic_from_ncu.py) so
+    that bench.py can tell when an ncu capture predates the kernels it describes."""
+    import hashlib
+    h = hashlib.sha1()
+    files = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
+    for f in files:
+        h.update(f.encode())
+        h.update(open(os.path.join(CSRC, f), "rb").read())
+    h.update(open(os.path.join(HERE, "..", "include", "surfel_b200.h"), "rb").read())
+    return h.hexdigest()
 
 
 def _stale(target, deps):

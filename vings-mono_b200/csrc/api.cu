@@ -89,6 +89,7 @@ const char* sb200_last_error(void) { return g_err; }
 size_t sb200_geom_bytes(int64_t P) { return sb_geom_layout(P).total; }
 size_t sb200_image_bytes(int W, int H) { return sb_image_layout(W, H).total; }
 size_t sb200_binning_bytes(int64_t R) { return sb_bin_layout(R).total; }
+size_t sb200_pair_list_bytes(int64_t R, int W, int H) { return sb_pair_list_layout(R, W, H).total; }
 size_t sb200_grad_bytes(int64_t P) { return sb_align((size_t)(P > 0 ? P : 0) * SB_GRAD_F * 4); }
 
 void sb200_geom_layout(int64_t P, size_t out[5]) {
@@ -224,7 +225,9 @@ static int forward_finish_impl(int P, int W, int H, int64_t R, int R_is_capacity
     }
     // with R == 0 every range is (0,0): the blend writes background / zeros, as the reference does
     StageScope sc(SB200_STAGE_BLEND_FWD, s);
-    return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others, s);
+    uint32_t* hit_masks = (uint32_t*)((char*)point_list + sb_pair_list_layout(R, W, H).masks);
+    return sb_launch_blend_forward(W, H, bg, (const char*)geom_ws, point_list, (char*)image_ws, out_color, out_others,
+                                   hit_masks, s);
 }
 
 int sb200_forward_finish(int P, int W, int H, int64_t R, const float* bg, void* geom_ws, void* binning_ws,
@@ -291,8 +294,9 @@ void sb200_sync_destroy(void* sync) {
     if (sync) cudaEventDestroy((cudaEvent_t)sync);
 }
 
-// test hook: per-tile cap of the backward walk for the calling thread's next backward calls (NULL = off)
-static thread_local const uint32_t* g_walk_cap = nullptr;
+// test hook: per-tile cap of the backward walk for the process's next backward calls (NULL = off).  Process-wide, not
+// thread-local: torch runs an autograd backward on its engine's worker thread, not on the thread that set the hook.
+static std::atomic<const uint32_t*> g_walk_cap{nullptr};
 
 static int backward_impl(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
                    const float* means3D, const float* scales, const float* rotations, const float* transmat,
@@ -318,7 +322,9 @@ static int backward_impl(int P, int W, int H, int64_t R, const float* bg, float 
         SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
         rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
                                       out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
-                                      (float*)grad_ws, g_walk_cap, s);
+                                      (float*)grad_ws,
+                                      (const uint32_t*)((const char*)point_list + sb_pair_list_layout(R, W, H).masks),
+                                      g_walk_cap.load(std::memory_order_acquire), s);
         if (rc) return rc;
     } else {
         SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
@@ -356,7 +362,7 @@ int sb200_backward_precomp(int P, int W, int H, int64_t R, const float* bg, floa
 }
 
 int sb200_debug_walk_cap(const uint32_t* per_tile_cap) {
-    g_walk_cap = per_tile_cap;
+    g_walk_cap.store(per_tile_cap, std::memory_order_release);
     return 0;
 }
 

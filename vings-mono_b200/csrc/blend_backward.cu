@@ -21,7 +21,15 @@
 //   * per hit surfel a 21-shuffle multi-value butterfly reduces the 20 gradient terms over the warp's 32
 //     pixels and 20 lanes issue ONE coalesced red.global.add.f32 over the surfel's 80-byte accumulation
 //     record (3 sectors); there is no cross-warp combine and no shared accumulation buffer;
-//   * every warp stops at ITS OWN last contributor (warp max), not the tile's.
+//   * every warp stops at ITS OWN last contributor (warp max), not the tile's;
+//   * round 2: NO culling here.  The forward blend already knows, per (32-surfel batch, warp), which surfels some live
+//     pixel of the warp's block may blend, and leaves that as one 32-bit hit mask per (batch, warp) behind the sorted
+//     id list (sb_pair_list_layout, common.cuh).  The ring's fill stages the batch's 8 mask words next to the ids,
+//     and a warp visits exactly the set bits: the box test, the two-at-a-time conic cull and their 3 LDS.128 per
+//     candidate (18 % of this kernel's instructions in round 1, profiles/r01_final_blend_backward_lines.txt) are
+//     gone.  A pixel joins a visit iff the surfel lies before its last contributor; every gate is then the
+//     reference's own arithmetic, so a pixel outside the surfel's footprint fails alpha >= 1/255 exactly as it does
+//     in the reference, which evaluates all 256 pixels of a tile for every surfel.
 #include "pair_math.cuh"
 #include "ring.cuh"
 
@@ -89,9 +97,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                          const uint32_t* __restrict__ n_contrib, const float* __restrict__ out_color,
                          const float* __restrict__ out_others, const float* __restrict__ dL_dpixels,
                          const float* __restrict__ dL_dothers, const bool* __restrict__ pixel_mask,
-                         float* __restrict__ grad_acc, const uint32_t* __restrict__ walk_cap) {
+                         float* __restrict__ grad_acc, const uint32_t* __restrict__ hit_masks,
+                         const uint32_t* __restrict__ walk_cap) {
     __shared__ __align__(128) float4 s_rec[BB_STAGES][BB_BATCH][SB_REC_F4];
     __shared__ uint32_t s_id[BB_STAGES][BB_BATCH];
+    __shared__ uint32_t s_mask[BB_STAGES][BB_CWARPS];
     __shared__ __align__(8) uint64_t s_full[BB_STAGES];
     __shared__ uint32_t s_done[BB_STAGES];
     __shared__ uint32_t s_maxlast[BB_CWARPS];
@@ -107,7 +117,6 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     // warp w owns the 8x4 block at (w&1, w>>1); lane l the pixel (l&7, l>>3) of it (as in the forward)
     const uint32_t wx0 = tx * SB_TILE_X + (wid & 1) * 8, wy0 = ty * SB_TILE_Y + (wid >> 1) * 4;
     const uint32_t px = wx0 + (lane & 7), py = wy0 + (lane >> 3);
-    const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
@@ -165,9 +174,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     int n_walk = min(n, (int)maxlast);
     // test hook (sb200_debug_walk_cap): stop where the reference's stored max_contrib makes ITS backward stop
     // (whole 32-surfel buckets at or beyond it are dropped, backward.cu:503-505; quirk Q17 in DESIGN.md)
-    if (walk_cap) n_walk = min(n_walk, (int)((walk_cap[tile] + BB_BATCH - 1) / BB_BATCH) * BB_BATCH);
+    // (the stored value can be stale shared memory, i.e. any 32-bit pattern: clamp before rounding up)
+    if (walk_cap) n_walk = min(n_walk, (int)((min(walk_cap[tile], 0x40000000u) + BB_BATCH - 1) / BB_BATCH) * BB_BATCH);
     const int nbatches = (n_walk + BB_BATCH - 1) / BB_BATCH;
 
+    const uint32_t* tile_masks = hit_masks + (size_t)sb_hit_slot(range.x, tile) * BB_CWARPS;
     // gather the records of batch b into ring stage b % BB_STAGES (called by one whole warp)
     auto fill = [&](int b) {
         const int st = b % BB_STAGES;
@@ -177,13 +188,15 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             id = __ldg(point_list + range.x + b * BB_BATCH + lane);
             s_id[st][lane] = id;
         }
+        if (lane < BB_CWARPS) s_mask[st][lane] = __ldg(tile_masks + (size_t)b * BB_CWARPS + lane);
         __syncwarp();
         if (lane == 0) bb_mbar_expect_tx(&s_full[st], (uint32_t)cnt * (SB_REC_F4 * 16));
         __syncwarp();
         if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
     };
     for (int b0 = wid; b0 < BB_STAGES && b0 < nbatches; b0 += BB_CWARPS) fill(b0);  // prime the ring
-    const int my_batches = (min(n_walk, (int)wmax) + BB_BATCH - 1) / BB_BATCH;
+    const int my_walk = min(n_walk, (int)wmax);   // this warp's pixels blend nothing at or behind this list position
+    const int my_batches = (my_walk + BB_BATCH - 1) / BB_BATCH;
 
     // running state
     float T = 1.f;              // transmittance as the backward propagates it
@@ -202,7 +215,6 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     for (int b = 0; b < nbatches; b++) {
         const int st = b % BB_STAGES;
         bb_mbar_wait(&s_full[st], (uint32_t)(b / BB_STAGES) & 1u);
-        const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
         if (b < my_batches) {
             // ---- bucket start: what the reference reloads from its checkpoint ----
             if (div) {
@@ -215,70 +227,17 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             M1b = M1;
             M2b = M2;
             const float4(*sr)[SB_REC_F4] = s_rec[st];
-            // warp-level cull: lane tests surfel `lane`'s box against the warp's 8x4 pixel block
-            bool ov = false;
-            if (lane < cnt) {
-                const float4 bb = sr[lane][SB_REC_BBOX];
-                ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
-#ifdef SB_BLOCK_CULL  // opt-in: measured neutral
-                if (ov) ov = !sb_block_culled(sr[lane][0], sr[lane][1], sr[lane][2], bx0, bx1, by0, by1);
-#endif
-            }
-            unsigned vm = __ballot_sync(0xffffffffu, ov);
-#ifdef SB_DEBUG_NO_WARP_CULL
-            vm = cnt >= 32 ? 0xffffffffu : ((1u << cnt) - 1u);
-#endif
-#ifndef SB_ONE_PHASE
-            // ---- phase 1: lane-level cull of every surviving surfel -> one pass bit per (lane, surfel) ----
-            // (division free, surfel_math.cuh: outside the alpha >= 1/255 footprint).  No vote and no branch
-            // depends on the arithmetic, and two surfels are evaluated per trip, so the LDS -> FFMA chains of
-            // neighbouring surfels overlap instead of serialising behind a per-surfel vote + branch.
-            uint32_t pm = 0;
-            while (vm) {
-                const int j0 = __ffs(vm) - 1;
-                vm &= vm - 1;
-                const int j1 = vm ? __ffs(vm) - 1 : j0;
-                vm &= vm - 1;  // (0 & anything stays 0)
-                const float4 a0 = sr[j0][0], a1 = sr[j0][1], a2 = sr[j0][2];
-                const float4 e0 = sr[j1][0], e1 = sr[j1][1], e2 = sr[j1][2];
-                const float dx0 = a0.w - pixf.x, dy0 = a1.w - pixf.y, dx1 = e0.w - pixf.x, dy1 = e1.w - pixf.y;
-                const float r0 = dx0 * dx0 + dy0 * dy0, r1 = dx1 * dx1 + dy1 * dy1;
-                const float qx0 = a2.x + a0.x * dx0 + a1.x * dy0, qx1 = e2.x + e0.x * dx1 + e1.x * dy1;
-                const float qy0 = a2.y + a0.y * dx0 + a1.y * dy0, qy1 = e2.y + e0.y * dx1 + e1.y * dy1;
-                const float qz0 = a2.z + a0.z * dx0 + a1.z * dy0, qz1 = e2.z + e0.z * dx1 + e1.z * dy1;
-                const float E0 = (qx0 * qx0 + qy0 * qy0) - a2.w * (qz0 * qz0);
-                const float E1 = (qx1 * qx1 + qy1 * qy1) - e2.w * (qz1 * qz1);
-                const bool p0 = !(E0 > 0.0f && (r0 + r0) > a2.w) && (uint32_t)(b * BB_BATCH + j0) < last;
-                const bool p1 = !(E1 > 0.0f && (r1 + r1) > e2.w) && (uint32_t)(b * BB_BATCH + j1) < last;
-                pm |= ((uint32_t)p0 << j0) | ((uint32_t)p1 << j1);
-            }
-            // ---- phase 2: the reference arithmetic, only for surfels some lane of the warp passes ----
-            uint32_t am = __reduce_or_sync(0xffffffffu, pm);
-#ifdef SB_DEBUG_NO_HEAVY
-            if (pm == 0xdeadbeefu) T += 1.f;
-            am = 0;
-#endif
+            // the surfels of this batch the forward marked for this warp, cut where the warp's walk ends: behind the
+            // warp's last contributor no pixel of the block is live (and a capped walk -- sb200_debug_walk_cap --
+            // ends on a batch boundary).  Below that limit every visit has at least one live pixel.
+            uint32_t am = s_mask[st][wid];
+            const int lim = my_walk - b * BB_BATCH;   // > 0 here
+            if (lim < BB_BATCH) am &= (1u << lim) - 1u;
             while (am) {
                 const int j = __ffs(am) - 1;
                 am &= am - 1;
-                const bool pass = (pm >> j) & 1u;
+                const bool pass = (uint32_t)(b * BB_BATCH + j) < last;
                 const float2 d = {sr[j][0].w - pixf.x, sr[j][1].w - pixf.y};
-#else
-            while (vm) {
-                const int j = __ffs(vm) - 1;
-                vm &= vm - 1;
-                const bool live = (uint32_t)(b * BB_BATCH + j) < last;
-                const float4 c0 = sr[j][0], c1 = sr[j][1], c2 = sr[j][2];
-                const float2 d = {c0.w - pixf.x, c1.w - pixf.y};
-                const float r2 = d.x * d.x + d.y * d.y;
-                const float qx = c2.x + c0.x * d.x + c1.x * d.y;
-                const float qy = c2.y + c0.y * d.x + c1.y * d.y;
-                const float qz = c2.z + c0.z * d.x + c1.z * d.y;
-                const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
-                const bool culled = E > 0.0f && (r2 + r2) > c2.w;
-                const bool pass = live && !culled;
-                if (!__any_sync(0xffffffffu, pass)) continue;
-#endif
                 float g[SB_GRAD_F];
 #pragma unroll
                 for (int i = 0; i < SB_GRAD_F; i++) g[i] = 0.f;
@@ -409,18 +368,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                         }
                     }
                 }
-#ifdef SB_DEBUG_NO_REDUCE
-                if (g[3] == 123.456f && g[17] == 1.0f && g[9] + g[19] + g[0] + g[14] + g[11] == 5.f) atomicAdd(grad_acc, g[1] + g[2] + g[4] + g[5] + g[6] + g[7] + g[8] + g[10] + g[12] + g[13] + g[15] + g[16] + g[18]);
-                hit = false;
-#endif
                 if (__any_sync(0xffffffffu, hit)) {
                     Butterfly<SB_GRAD_F, 16>::run(g, lane);
                     // 20 lanes, 20 consecutive floats of the surfel's accumulation record: one coalesced RED
-#ifdef SB_DEBUG_NO_ATOMIC
-                    if (slot >= 0 && g[0] == 123.456f)
-#else
                     if (slot >= 0)
-#endif
                         atomicAdd(grad_acc + (size_t)s_id[st][j] * SB_GRAD_F + slot, g[0]);
                 }
             }
@@ -444,13 +395,13 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                              const char* image, const float* out_color, const float* out_others,
                              const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
-                             float* grad_acc, const uint32_t* walk_cap, cudaStream_t s) {
+                             float* grad_acc, const uint32_t* hit_masks, const uint32_t* walk_cap, cudaStream_t s) {
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
     sb_blend_backward_kernel<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
-        dL_dcolor, dL_dothers, pixel_mask, grad_acc, walk_cap);
+        dL_dcolor, dL_dothers, pixel_mask, grad_acc, hit_masks, walk_cap);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(FB_THREADS)
 sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                         const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                        float* __restrict__ out_color, float* __restrict__ out_others) {
+                        float* __restrict__ out_color, float* __restrict__ out_others, uint32_t* __restrict__ hit_masks) {
     __shared__ __align__(128) float4 s_rec[FB_STAGES][FB_BATCH][SB_REC_F4];
     __shared__ __align__(8) uint64_t s_full[FB_STAGES];
     __shared__ uint32_t s_cnt[FB_STAGES];
@@ -50,12 +50,21 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
+    // the block's pixel-centre ranges along x, y, x+y, x-y, saturated like the records' int16 bounds
+    const int kx0 = min((int)wx0, 32767), kx1 = min((int)wx0 + 7, 32767), ky0 = min((int)wy0, 32767), ky1 = min((int)wy0 + 3, 32767);
+    const int ks0 = min((int)(wx0 + wy0), 32767), ks1 = min((int)(wx0 + wy0) + 10, 32767);
+    const int kd0 = max(min((int)wx0 - (int)wy0 - 3, 32767), -32768), kd1 = max(min((int)wx0 - (int)wy0 + 7, 32767), -32768);
+#ifdef SB_BLOCK_CULL
     const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
+#endif
     bool done = !inside;
 
     const uint2 range = ranges[tile];
     const int n = (int)(range.y - range.x);
     const int nbatches = (n + FB_BATCH - 1) / FB_BATCH;
+    // hit-mask words of this tile's batches (sb_hit_slot, common.cuh): one word per (batch, warp) = the surfels of the
+    // batch some live pixel of the warp's block may blend.  The backward walks exactly those (blend_backward.cu).
+    uint32_t* my_masks = hit_masks + ((size_t)sb_hit_slot(range.x, tile) * FB_WARPS + wid);
 
     if (tid < FB_STAGES) {
         bb_mbar_init(&s_full[tid], 1);
@@ -103,16 +112,24 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         if (!wdone) {
             const int c = 0;
             // ---- warp-level cull: lane tests surfel c+lane's box against the warp's pixel block ----
+            // (measured and dropped, round 2, tools/time_stages.py A/B on C2-C5: shrinking the block to the bounding box of
+            // its still-live pixels is neutral; a four-corner "footprint contains the whole block" test that skips phase 1
+            // costs 12-14 % at C4/C5 -- the synthetic clouds' randomly oriented surfels project to thin ellipses that
+            // rarely contain an 8x4 block)
             bool ov = false;
             if (c + lane < cnt) {
-                const float4 bb = sq[c + lane][SB_REC_BBOX];
-                ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+                // footprint bounds along x, y and the two diagonals against the block's ranges (8 int16 per record)
+                const float4 bf = sq[c + lane][SB_REC_BBOX];
+                const int b0 = __float_as_int(bf.x), b1 = __float_as_int(bf.y), b2 = __float_as_int(bf.z), b3 = __float_as_int(bf.w);
+                ov = (int)(short)b0 <= kx1 && (b0 >> 16) >= kx0 && (int)(short)b1 <= ky1 && (b1 >> 16) >= ky0;
+#ifndef FB_NO_DIAG
+                ov = ov && (int)(short)b2 <= ks1 && (b2 >> 16) >= ks0 && (int)(short)b3 <= kd1 && (b3 >> 16) >= kd0;
+#endif
 #ifdef SB_BLOCK_CULL  // opt-in: measured neutral
                 if (ov) ov = !sb_block_culled(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bx0, bx1, by0, by1);
 #endif
             }
             unsigned m = __ballot_sync(0xffffffffu, ov);
-#ifndef SB_ONE_PHASE
             // ---- phase 1: lane-level cull (division free) of every surviving surfel -> one pass bit per
             // (lane, surfel); two surfels per trip and no vote / branch on the arithmetic, so the LDS -> FFMA
             // chains overlap ----
@@ -138,26 +155,15 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
             if (done) pm = 0;
             // ---- phase 2: surfels some live lane of the warp passes ----
             uint32_t am = __reduce_or_sync(0xffffffffu, pm);
+#ifndef FB_NO_MASK_STORE   // (timing experiments only: the backward needs the masks)
+            if (lane == 0) my_masks[(size_t)b * FB_WARPS] = am;
+#endif
             while (am) {
                 const int jj = __ffs(am) - 1;
                 const int j = c + jj;
                 am &= am - 1;
                 if (done || !((pm >> jj) & 1u)) continue;
                 const float2 d = {sq[j][0].w - pixf.x, sq[j][1].w - pixf.y};  // == the reference's d (forward.cu:413)
-#else
-            while (m) {
-                const int j = c + __ffs(m) - 1;
-                m &= m - 1;
-                // ---- lane-level cull (division free) ----
-                const float4 c0 = sq[j][0], c1 = sq[j][1], c2 = sq[j][2];
-                const float2 d = {c0.w - pixf.x, c1.w - pixf.y};  // == the reference's d (forward.cu:413)
-                const float r2 = d.x * d.x + d.y * d.y;
-                const float qx = c2.x + c0.x * d.x + c1.x * d.y;
-                const float qy = c2.y + c0.y * d.x + c1.y * d.y;
-                const float qz = c2.z + c0.z * d.x + c1.z * d.y;
-                const float E = (qx * qx + qy * qy) - c2.w * (qz * qz);
-                if (done || (E > 0.0f && (r2 + r2) > c2.w)) continue;
-#endif
                 // ---- the reference's arithmetic (forward.cu:401-468) ----
                 const float4 q3 = sq[j][SB_REC_TU], q4 = sq[j][SB_REC_TV], q5 = sq[j][SB_REC_TW];
                 const float3 Tu = {q3.x, q3.y, q3.z}, Tv = {q4.x, q4.y, q4.z}, Tw = {q5.x, q5.y, q5.z};
@@ -246,13 +252,13 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
 }
 
 int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
-                            char* image, float* out_color, float* out_others, cudaStream_t s) {
+                            char* image, float* out_color, float* out_others, uint32_t* hit_masks, cudaStream_t s) {
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
     // geom layout: the record array is first and its offset does not depend on P
     sb_blend_forward_kernel<<<grid_x * grid_y, FB_THREADS, 0, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
-        (float*)(image + IL.final_T), (uint32_t*)(image + IL.n_contrib), out_color, out_others);
+        (float*)(image + IL.final_T), (uint32_t*)(image + IL.n_contrib), out_color, out_others, hit_masks);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

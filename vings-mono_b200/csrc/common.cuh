@@ -27,7 +27,8 @@
 //   q4 = (Tv.x, Tv.y, Tv.z, r)
 //   q5 = (Tw.x, Tw.y, Tw.z, g)
 //   q6 = (n.x,  n.y,  n.z,  b)
-//   q7 = (xmin, xmax, ymin, ymax)      pixel-space box outside of which the surfel cannot reach alpha >= 1/255
+//   q7 = 8 x int16: min | max << 16 along x, y, x+y, x-y   pixel-space bounds outside of which the surfel cannot
+//                                      reach alpha >= 1/255 (surfel_math.cuh, SbCull::dop)
 #define SB_REC_F4 8
 #define SB_REC_CULL 0
 #define SB_REC_TU 3
@@ -122,6 +123,26 @@ static inline __host__ SbImageLayout sb_image_layout(int W, int H) {
     return L;
 }
 
+// Pair list (caller-allocated, persists forward -> backward): the sorted surfel ids, then the forward's hit masks.
+//   ids    uint32[R]                      `point_list`
+//   masks  uint32[slots * 8]              one word per (32-surfel batch of a tile, warp of the tile's CTA): bit j =
+//                                         "some live pixel of the warp's 8x4 block may blend surfel j of the batch"
+// Batch b of tile t (whose list starts at position x_t) owns slot  (x_t >> 5) + t + b : distinct for distinct (t, b)
+// because floor(x/32) + ceil(n/32) <= floor((x+n)/32) + 1, and below R/32 + tiles + 1.
+struct SbPairListLayout { size_t ids, masks, total; };
+static inline __host__ SbPairListLayout sb_pair_list_layout(int64_t R, int W, int H) {
+    SbPairListLayout L;
+    size_t r = (size_t)(R > 0 ? R : 0);
+    size_t tiles = (size_t)((W + SB_TILE_X - 1) / SB_TILE_X) * ((H + SB_TILE_Y - 1) / SB_TILE_Y);
+    L.ids = 0;
+    L.masks = sb_align(r * 4);
+    L.total = sb_align(L.masks + (r / 32 + tiles + 2) * 8 * 4);
+    return L;
+}
+static inline __host__ __device__ uint32_t sb_hit_slot(uint32_t list_begin, uint32_t tile) {
+    return (list_begin >> 5) + tile;
+}
+
 // Binning scratch (caller-allocated, R-sized; only point_list survives the forward and it is a
 // separate caller buffer).
 struct SbBinLayout {
@@ -173,6 +194,15 @@ static inline __host__ uint32_t sb_higher_msb(uint32_t n) {
     return msb;
 }
 
+// Masked Adam without bias correction, one scalar (DSR/cuda_rasterizer/adam.cu:26-37).  One definition for the three
+// kernels that apply it (sb_adam_kernel, sb_surfel_update_kernel, sb_dp_post_kernel): the same expression tree, so
+// nvcc contracts it the same way and the single-GPU pass, the NCCL path and the peer-memory path round identically.
+__device__ __forceinline__ void sb_adam_scalar(float& p, float& m, float& v, float g, float lr, float b1, float b2, float eps) {
+    m = b1 * m + (1.0f - b1) * g;
+    v = b2 * v + (1.0f - b2) * g * g;
+    p += -lr * m / (sqrtf(v) + eps);
+}
+
 #define SB_MAX_DEVICES 64
 static inline int sb_current_device() {
     int dev = 0;
@@ -214,11 +244,11 @@ int sb_launch_sort_passes(const SbSortPlan& pl, int small, const uint32_t* keys_
 int sb_launch_tile_scan(int tiles, const SbSortPlan& pl, const uint32_t* tile_counts, uint2* ranges, uint32_t* order,
                         uint32_t* digit_base, cudaStream_t s);
 int sb_launch_blend_forward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
-                            char* image, float* out_color, float* out_others, cudaStream_t s);
+                            char* image, float* out_color, float* out_others, uint32_t* hit_masks, cudaStream_t s);
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,
                              const char* image, const float* out_color, const float* out_others,
                              const float* dL_dcolor, const float* dL_dothers, const bool* pixel_mask,
-                             float* grad_acc, const uint32_t* walk_cap, cudaStream_t s);
+                             float* grad_acc, const uint32_t* hit_masks, const uint32_t* walk_cap, cudaStream_t s);
 int sb_launch_preprocess_backward(int P, int W, int H, float tanfovx, float tanfovy, const float* means3D,
                                   const float* scales, const float* rotations, const float* transmat_precomp,
                                   const float* viewmatrix,

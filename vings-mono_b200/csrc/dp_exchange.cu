@@ -1,0 +1,309 @@
+// Multi-GPU exchange of the mapping step, written against NVLink peer memory.
+//
+// The keyframe window's views are partitioned over the ranks of one box, surfels and Adam state are replicated.
+// Every optimizer step each rank has rendered ONE view; per surfel the step needs the sum over the ranks' views of
+// the (score-weighted) raw-parameter gradients, the score bookkeeping of every view and the union of the
+// visibilities.  Round 1 did that with a dense NCCL all-reduce of a [16,P] fp32 buffer (64 B per surfel per rank,
+// 60 % of it zeros: a view sees ~40 % of the cloud), fully exposed between two per-surfel kernels.
+//
+// Here the exchange is three kernels over peer-mapped ("symmetric") buffers -- the compute and the collective are
+// the same launches, only rows of surfels a view actually saw ever cross NVLink, and no reduction order depends on
+// the rank that reads the result:
+//
+//   sb_dp_stage_kernel   (every rank, all surfels)   backward of the three activations; a visible surfel's 13
+//                        raw-parameter gradients + its two scores go into the rank's OWN stage row (64 B), its
+//                        visibility into a byte array.  Local stores only.
+//   -- barrier over the ranks (signal pads of the symmetric allocation; Python side) --
+//   sb_dp_reduce_kernel  (rank r, its slice of the surfels)   a reduce-scatter by peer LOADS: for the surfels it
+//                        owns the rank reads the stage rows of the ranks that saw them, applies weighting_grad per
+//                        view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views IN RANK ORDER into one
+//                        80-B result row: gradient sum, add_records' running quantities (gaussian_model.py:163-168:
+//                        score sum, max of the second score, first arg-max of the first score and its keyframe id).
+//   -- barrier --
+//   sb_dp_post_kernel    (every rank, all surfels)   an all-gather fused with its consumer: reads the result row of
+//                        every touched surfel from its owner (peer load for 7/8 of them) and applies the score
+//                        bookkeeping and the masked Adam step to the local replica.  Every rank consumes the same
+//                        80 bytes, so the replicas stay bit-identical by construction.
+//
+// Bytes over NVLink per rank and step at C2 on 8 GPUs: stage rows 7/8 * (P/8) * 8 * 0.41 * 64 B = 22 MB in, result
+// rows 7/8 * ~0.6 P * 80 B = 50 MB in, against 2 * 7/8 * 77 MB = 134 MB for the dense all-reduce.
+#include "common.cuh"
+#include "../../include/surfel_b200.h"
+
+#define SB_DP_MAX_RANKS 16
+#define SB_DP_STAGE_F 16   // floats per stage row: 13 gradients, score 0, score 1, pad
+#define SB_DP_OUT_F 20     // floats per result row: 13 gradients, score sum, score-1 max, score-0 max, kf id (2 words), pad 2
+
+// Loads of memory another GPU wrote in an earlier kernel (ordered by the ranks' barrier): system-scope relaxed loads,
+// never served from this SM's L1.
+__device__ __forceinline__ float4 sb_ld_sys_f4(const float4* p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ uint32_t sb_ld_sys_u8(const uint8_t* p) {
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+struct SbDpStageArgs {
+    const float* d_means3D; const float* d_colors; const float* d_opacity; const float* d_scales; const float* d_rot;
+    const float* cur_scores; const int* radii;
+    const float* opacity_raw; const float* scaling_raw; const float* rotation_raw;
+    float* stage; uint8_t* vis;
+    int P;
+};
+
+__global__ void __launch_bounds__(256) sb_dp_stage_kernel(SbDpStageArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.P) return;
+    const bool visible = a.radii[i] > 0;
+    a.vis[i] = visible ? 1 : 0;
+    if (!visible) return;
+    const size_t iz = (size_t)i;
+    float g[13];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        g[k] = a.d_means3D[3 * iz + k];
+        g[3 + k] = a.d_colors[3 * iz + k];
+    }
+    g[6] = a.d_opacity[i];
+    const float2 ds = ((const float2*)a.d_scales)[i];
+    const float4 dq = ((const float4*)a.d_rot)[i];
+    const float2 cs = ((const float2*)a.cur_scores)[i];
+    const float o_raw = a.opacity_raw[i];
+    const float2 s_raw = ((const float2*)a.scaling_raw)[i];
+    const float4 q = ((const float4*)a.rotation_raw)[i];
+    // ---- backward of sigmoid / exp / normalize: the same expressions as sb_surfel_update_kernel (surfel_update.cu) ----
+    const float y = 1.0f / (1.0f + expf(-o_raw));
+    g[6] = g[6] * (1.0f - y) * y;
+    g[7] = ds.x * expf(s_raw.x);
+    g[8] = ds.y * expf(s_raw.y);
+    const float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    if (len > 1e-12f) {
+        const float4 r = make_float4(q.x / len, q.y / len, q.z / len, q.w / len);
+        const float rd = r.x * dq.x + r.y * dq.y + r.z * dq.z + r.w * dq.w;
+        g[9] = (dq.x - r.x * rd) / len; g[10] = (dq.y - r.y * rd) / len;
+        g[11] = (dq.z - r.z * rd) / len; g[12] = (dq.w - r.w * rd) / len;
+    } else {
+        g[9] = dq.x / 1e-12f; g[10] = dq.y / 1e-12f; g[11] = dq.z / 1e-12f; g[12] = dq.w / 1e-12f;
+    }
+    float4* row = (float4*)(a.stage + iz * SB_DP_STAGE_F);
+    row[0] = make_float4(g[0], g[1], g[2], g[3]);
+    row[1] = make_float4(g[4], g[5], g[6], g[7]);
+    row[2] = make_float4(g[8], g[9], g[10], g[11]);
+    row[3] = make_float4(g[12], cs.x, cs.y, 0.0f);
+}
+
+struct SbDpReduceArgs {
+    const float* peer_stage[SB_DP_MAX_RANKS];
+    const uint8_t* peer_vis[SB_DP_MAX_RANKS];
+    long long kf_ids[SB_DP_MAX_RANKS];
+    const float* global_scores;   // [P,2] local replica (identical on every rank)
+    float* out;                   // [slice, SB_DP_OUT_F] this rank's result rows
+    uint8_t* upd;                 // [slice] 1 = some view saw the surfel
+    int lo, hi, n_ranks;
+};
+
+__global__ void __launch_bounds__(256) sb_dp_reduce_kernel(SbDpReduceArgs a) {
+    const int i = a.lo + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.hi) return;
+    const size_t iz = (size_t)i;
+    const float glob0 = a.global_scores[2 * iz];
+    float acc[13];
+#pragma unroll
+    for (int c = 0; c < 13; c++) acc[c] = 0.0f;
+    float s0_sum = 0.0f, s1_max = 0.0f, s0_max = -1.0f;
+    long long kf_arg = 0;
+    bool any = false;
+    for (int q = 0; q < a.n_ranks; q++) {   // rank order = the order a single process would take the views in
+        if (!sb_ld_sys_u8(a.peer_vis[q] + iz)) continue;
+        const float4* row = (const float4*)(a.peer_stage[q] + iz * SB_DP_STAGE_F);
+        const float4 r0 = sb_ld_sys_f4(row), r1 = sb_ld_sys_f4(row + 1), r2 = sb_ld_sys_f4(row + 2), r3 = sb_ld_sys_f4(row + 3);
+        const float c0 = r3.y, c1 = r3.z;
+        // weighting_grad with this view's score counted into the global score (add_records runs first), as in the
+        // single-GPU pass; the global score itself is updated once, from the sum, by sb_dp_post_kernel
+        const float gw = c0 / (fminf(fmaxf(glob0 + c0, 0.0f), 1e4f) + 1e-6f + c0);
+        const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
+#pragma unroll
+        for (int c = 0; c < 13; c++) acc[c] = __fadd_rn(acc[c], __fmul_rn(g[c], gw));   // a plain sum of the views' weighted rows
+        s0_sum += c0;
+        s1_max = fmaxf(s1_max, c1);
+        if (c0 > s0_max) { s0_max = c0; kf_arg = a.kf_ids[q]; }   // strict: the first view holding the maximum keeps it
+        any = true;
+    }
+    const int li = i - a.lo;
+    a.upd[li] = any ? 1 : 0;
+    if (!any) return;
+    float4* o = (float4*)(a.out + (size_t)li * SB_DP_OUT_F);
+    o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+    o[2] = make_float4(acc[8], acc[9], acc[10], acc[11]);
+    o[3] = make_float4(acc[12], s0_sum, s1_max, s0_max);
+    o[4] = make_float4(__int_as_float((int)(kf_arg & 0xffffffffll)), __int_as_float((int)(kf_arg >> 32)), 0.0f, 0.0f);
+}
+
+struct SbDpPostArgs {
+    const float* peer_out[SB_DP_MAX_RANKS];
+    const uint8_t* peer_upd[SB_DP_MAX_RANKS];
+    float* param[5]; float* m[5]; float* v[5];
+    const uint8_t* stable;
+    float* local_scores; float* global_scores; float* kf_max; long long* kf_id;
+    float lr[5];
+    float b1, b2, eps;
+    int P, slice;
+};
+
+#define SB_GRP(c) ((c) < 3 ? 0 : (c) < 6 ? 1 : (c) < 7 ? 2 : (c) < 9 ? 3 : 4)
+#define SB_GRP_NC(g) ((g) == 0 ? 3 : (g) == 1 ? 3 : (g) == 2 ? 1 : (g) == 3 ? 2 : 4)
+#define SB_GRP_C0(g) ((g) == 0 ? 0 : (g) == 1 ? 3 : (g) == 2 ? 6 : (g) == 3 ? 7 : 9)
+
+__global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.P) return;
+    const size_t iz = (size_t)i;
+    const int owner = i / a.slice, li = i - owner * a.slice;
+    if (!sb_ld_sys_u8(a.peer_upd[owner] + li)) return;   // no view saw it: add_records with zero scores is the identity
+    const float4* o = (const float4*)(a.peer_out[owner] + (size_t)li * SB_DP_OUT_F);
+    const float4 r0 = sb_ld_sys_f4(o), r1 = sb_ld_sys_f4(o + 1), r2 = sb_ld_sys_f4(o + 2), r3 = sb_ld_sys_f4(o + 3),
+                 r4 = sb_ld_sys_f4(o + 4);
+    const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
+    const float s0_sum = r3.y, s1_max = r3.z, s0_max = r3.w;
+    const long long kf_arg = ((long long)__float_as_int(r4.y) << 32) | (unsigned int)__float_as_int(r4.x);
+    const bool adam = !a.stable[i];
+
+    // ---- every load before the first store (see sb_surfel_update_kernel) ----
+    const float glob0 = a.global_scores[2 * iz], glob1 = a.global_scores[2 * iz + 1];
+    const float loc0 = a.local_scores[2 * iz], loc1 = a.local_scores[2 * iz + 1], kfm = a.kf_max[i];
+    float pv[13], mv[13], vv[13];
+    if (adam) {
+#pragma unroll
+        for (int c = 0; c < 7; c++) {
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+            pv[c] = a.param[grp][e]; mv[c] = a.m[grp][e]; vv[c] = a.v[grp][e];
+        }
+        const float2 s2 = ((const float2*)a.param[3])[i], ms2 = ((const float2*)a.m[3])[i], vs2 = ((const float2*)a.v[3])[i];
+        const float4 q4 = ((const float4*)a.param[4])[i], mq4 = ((const float4*)a.m[4])[i], vq4 = ((const float4*)a.v[4])[i];
+        pv[7] = s2.x; pv[8] = s2.y; mv[7] = ms2.x; mv[8] = ms2.y; vv[7] = vs2.x; vv[8] = vs2.y;
+        pv[9] = q4.x; pv[10] = q4.y; pv[11] = q4.z; pv[12] = q4.w;
+        mv[9] = mq4.x; mv[10] = mq4.y; mv[11] = mq4.z; mv[12] = mq4.w;
+        vv[9] = vq4.x; vv[10] = vq4.y; vv[11] = vq4.z; vv[12] = vq4.w;
+    }
+
+    // ---- add_records of the step's views, folded (gaussian_model.py:163-168, gaussian_base.py:388-392) ----
+    a.local_scores[2 * iz] = loc0 + s0_sum;
+    if (s1_max > loc1) a.local_scores[2 * iz + 1] = s1_max;
+    a.global_scores[2 * iz] = fminf(fmaxf(glob0 + s0_sum, 0.0f), 1e4f);
+    a.global_scores[2 * iz + 1] = fminf(fmaxf(glob1, 0.0f), 1e4f);
+    if (kfm < s0_max) {
+        a.kf_max[i] = s0_max;
+        a.kf_id[i] = kf_arg;
+    }
+
+    // ---- masked Adam without bias correction (adam.cu:9-38) ----
+    if (adam) {
+        float pn[13], mn[13], vn[13];
+#pragma unroll
+        for (int c = 0; c < 13; c++) {
+            pn[c] = pv[c]; mn[c] = mv[c]; vn[c] = vv[c];
+            sb_adam_scalar(pn[c], mn[c], vn[c], g[c], a.lr[SB_GRP(c)], a.b1, a.b2, a.eps);
+        }
+#pragma unroll
+        for (int c = 0; c < 7; c++) {
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+            a.param[grp][e] = pn[c]; a.m[grp][e] = mn[c]; a.v[grp][e] = vn[c];
+        }
+        ((float2*)a.param[3])[i] = make_float2(pn[7], pn[8]);
+        ((float2*)a.m[3])[i] = make_float2(mn[7], mn[8]);
+        ((float2*)a.v[3])[i] = make_float2(vn[7], vn[8]);
+        ((float4*)a.param[4])[i] = make_float4(pn[9], pn[10], pn[11], pn[12]);
+        ((float4*)a.m[4])[i] = make_float4(mn[9], mn[10], mn[11], mn[12]);
+        ((float4*)a.v[4])[i] = make_float4(vn[9], vn[10], vn[11], vn[12]);
+    }
+}
+
+extern "C" {
+
+size_t sb200_dp_stage_bytes(int64_t P) { return sb_align((size_t)(P > 0 ? P : 0) * SB_DP_STAGE_F * 4); }
+size_t sb200_dp_out_bytes(int64_t slice) { return sb_align((size_t)(slice > 0 ? slice : 0) * SB_DP_OUT_F * 4); }
+
+int sb200_dp_stage(int P, const float* d_means3D, const float* d_colors, const float* d_opacity, const float* d_scales,
+                   const float* d_rotations, const float* cur_scores, const int* radii, const float* opacity_raw,
+                   const float* scaling_raw, const float* rotation_raw, float* stage, uint8_t* vis, void* stream) {
+    if (P < 0) { sb_set_error("dp_stage: bad P"); return 1; }
+    if (P == 0) return 0;
+    if (!d_means3D || !d_colors || !d_opacity || !d_scales || !d_rotations || !cur_scores || !radii || !opacity_raw ||
+        !scaling_raw || !rotation_raw || !stage || !vis) { sb_set_error("dp_stage: NULL input"); return 1; }
+    if ((((uintptr_t)d_scales | (uintptr_t)cur_scores | (uintptr_t)scaling_raw) & 7) ||
+        (((uintptr_t)d_rotations | (uintptr_t)rotation_raw | (uintptr_t)stage) & 15)) {
+        sb_set_error("dp_stage: [P,2] arrays must be 8-byte, [P,4] arrays and the stage rows 16-byte aligned");
+        return 1;
+    }
+    SbDpStageArgs a = {d_means3D, d_colors, d_opacity, d_scales, d_rotations, cur_scores, radii,
+                       opacity_raw, scaling_raw, rotation_raw, stage, vis, P};
+    cudaStream_t s = (cudaStream_t)stream;
+    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    sb_dp_stage_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int sb200_dp_reduce(int lo, int hi, int n_ranks, const void* const* peer_stage, const void* const* peer_vis,
+                    const int64_t* kf_ids, const float* global_scores, float* out, uint8_t* upd, void* stream) {
+    if (lo < 0 || hi < lo || n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS) { sb_set_error("dp_reduce: bad slice / rank count"); return 1; }
+    if (hi == lo) return 0;
+    if (!peer_stage || !peer_vis || !kf_ids || !global_scores || !out || !upd) { sb_set_error("dp_reduce: NULL input"); return 1; }
+    SbDpReduceArgs a;
+    for (int q = 0; q < n_ranks; q++) {
+        if (!peer_stage[q] || !peer_vis[q]) { sb_set_error("dp_reduce: NULL peer buffer %d", q); return 1; }
+        a.peer_stage[q] = (const float*)peer_stage[q];
+        a.peer_vis[q] = (const uint8_t*)peer_vis[q];
+        a.kf_ids[q] = kf_ids[q];
+    }
+    a.global_scores = global_scores; a.out = out; a.upd = upd; a.lo = lo; a.hi = hi; a.n_ranks = n_ranks;
+    cudaStream_t s = (cudaStream_t)stream;
+    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    sb_dp_reduce_kernel<<<(hi - lo + 255) / 256, 256, 0, s>>>(a);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+int sb200_dp_post(int P, int slice, int n_ranks, const void* const* peer_out, const void* const* peer_upd,
+                  float* const* params, float* const* exp_avg, float* const* exp_avg_sq, const uint8_t* stable_mask,
+                  float* local_scores, float* global_scores, float* kf_max_scores, int64_t* kf_id, const float* lr,
+                  float b1, float b2, float eps, void* stream) {
+    if (P < 0 || slice < 1 || n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS || (int64_t)slice * n_ranks < P) {
+        sb_set_error("dp_post: bad P / slice / rank count");
+        return 1;
+    }
+    if (P == 0) return 0;
+    if (!peer_out || !peer_upd || !params || !exp_avg || !exp_avg_sq || !stable_mask || !local_scores ||
+        !global_scores || !kf_max_scores || !kf_id || !lr) { sb_set_error("dp_post: NULL input"); return 1; }
+    if ((((uintptr_t)params[3] | (uintptr_t)exp_avg[3] | (uintptr_t)exp_avg_sq[3]) & 7) ||
+        (((uintptr_t)params[4] | (uintptr_t)exp_avg[4] | (uintptr_t)exp_avg_sq[4]) & 15)) {
+        sb_set_error("dp_post: scaling arrays must be 8-byte, rotation arrays 16-byte aligned");
+        return 1;
+    }
+    SbDpPostArgs a;
+    for (int q = 0; q < n_ranks; q++) {
+        if (!peer_out[q] || !peer_upd[q]) { sb_set_error("dp_post: NULL peer buffer %d", q); return 1; }
+        a.peer_out[q] = (const float*)peer_out[q];
+        a.peer_upd[q] = (const uint8_t*)peer_upd[q];
+    }
+    for (int g = 0; g < 5; g++) { a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g]; }
+    a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;
+    a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.slice = slice;
+    cudaStream_t s = (cudaStream_t)stream;
+    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    sb_dp_post_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"

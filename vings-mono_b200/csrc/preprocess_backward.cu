@@ -186,10 +186,9 @@ __global__ void sb_adam_kernel(float* __restrict__ param, const float* __restric
         float g = grad[p_idx];
         float m = exp_avg[p_idx];
         float v = exp_avg_sq[p_idx];
-        m = b1 * m + (1.0f - b1) * g;
-        v = b2 * v + (1.0f - b2) * g * g;
-        float step = -lr * m / (sqrt(v) + eps);
-        param[p_idx] += step;
+        float p = param[p_idx];
+        sb_adam_scalar(p, m, v, g, lr, b1, b2, eps);
+        param[p_idx] = p;
         exp_avg[p_idx] = m;
         exp_avg_sq[p_idx] = v;
     }

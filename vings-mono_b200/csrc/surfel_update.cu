@@ -197,10 +197,8 @@ __global__ void __launch_bounds__(256) sb_surfel_update_kernel(SbUpdateArgs a) {
         float pn[13], mn[13], vn[13];
 #pragma unroll
         for (int c = 0; c < 13; c++) {
-            const int grp = SB_GRP(c);
-            mn[c] = a.b1 * mv[c] + (1.0f - a.b1) * g[c];
-            vn[c] = a.b2 * vv[c] + (1.0f - a.b2) * g[c] * g[c];
-            pn[c] = pv[c] + -a.lr[grp] * mn[c] / (sqrtf(vn[c]) + a.eps);
+            pn[c] = pv[c]; mn[c] = mv[c]; vn[c] = vv[c];
+            sb_adam_scalar(pn[c], mn[c], vn[c], g[c], a.lr[SB_GRP(c)], a.b1, a.b2, a.eps);
         }
 #pragma unroll
         for (int c = 0; c < 7; c++) {

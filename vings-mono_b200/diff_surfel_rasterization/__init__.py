@@ -50,6 +50,8 @@ def _load():
         getattr(lib, name).argtypes = [_i64]
     lib.sb200_image_bytes.restype = _sz
     lib.sb200_image_bytes.argtypes = [_i32, _i32]
+    lib.sb200_pair_list_bytes.restype = _sz
+    lib.sb200_pair_list_bytes.argtypes = [_i64, _i32, _i32]
     lib.sb200_geom_layout.argtypes = [_i64, ctypes.POINTER(_sz)]
     lib.sb200_geom_layout.restype = None
     lib.sb200_image_layout.argtypes = [_i32, _i32, ctypes.POINTER(_sz)]
@@ -100,6 +102,16 @@ def _load():
     lib.sb200_surfel_update.restype = _i32
     lib.sb200_surfel_update.argtypes = ([_i32, _i32] + [_vp] * 3 + [_vp] * 5 + [_vp] * 7 + [_i64, _vp, _vp] +
                                         [_f32] * 3 + [_vp])
+    lib.sb200_dp_stage_bytes.restype = _sz
+    lib.sb200_dp_stage_bytes.argtypes = [_i64]
+    lib.sb200_dp_out_bytes.restype = _sz
+    lib.sb200_dp_out_bytes.argtypes = [_i64]
+    lib.sb200_dp_stage.restype = _i32
+    lib.sb200_dp_stage.argtypes = [_i32] + [_vp] * 13
+    lib.sb200_dp_reduce.restype = _i32
+    lib.sb200_dp_reduce.argtypes = [_i32, _i32, _i32] + [_vp] * 7
+    lib.sb200_dp_post.restype = _i32
+    lib.sb200_dp_post.argtypes = [_i32, _i32, _i32] + [_vp] * 11 + [_f32] * 3 + [_vp]
     lib.sb200_knn_mean_dist2.restype = _i32
     lib.sb200_knn_mean_dist2.argtypes = [_i32, _vp, _vp, _vp]
     lib.sb200_prune_scratch_bytes.restype = _sz
@@ -171,6 +183,7 @@ class _Workspace:
             self.geom, self.geom_P = u8(lib.sb200_geom_bytes(cap)), cap
         if self.image_WH != (W, H):
             self.image, self.image_WH = u8(lib.sb200_image_bytes(W, H)), (W, H)
+            self.pair_capacity = 0   # the pair list holds per-tile hit masks: sized for one image size
 
     def fit_grad(self, P):
         if P > self.grad_P:
@@ -179,11 +192,14 @@ class _Workspace:
             self.grad_P = cap
 
     def grow_pairs(self, R):
+        """Binning scratch and pair list (sorted ids + hit masks) for up to 1.25 R pairs at the current image size."""
         lib = _load()
         want = int(R * 1.25) + 4096
+        W, H = self.image_WH
         self.binning = torch.empty(lib.sb200_binning_bytes(want), dtype=torch.uint8, device=self.device)
-        self.point_list = torch.empty(want, dtype=torch.int32, device=self.device)
+        self.point_list = torch.empty(lib.sb200_pair_list_bytes(want, W, H), dtype=torch.uint8, device=self.device)
         self.pair_capacity = want
+        self.pair_WH = (W, H)
 
 
 class _Lease:
@@ -331,7 +347,7 @@ class _RasterizeGaussians(torch.autograd.Function):
             return R
 
         if ctx.use_pre or ws.pair_capacity < 1:
-            R = two_stage()
+            R = R_arg = two_stage()
         else:
             # sync-free forward on the scratch kept from earlier calls: the whole forward is queued at once and the
             # host only waits for the pair count (copied back right behind the preprocess) to confirm that the
@@ -343,15 +359,15 @@ class _RasterizeGaussians(torch.autograd.Function):
                                            _ptr(ws.image), _ptr(color), _ptr(others), _vp(ws.count.data_ptr()),
                                            _vp(ws.sync), stream), "sb200_forward_async")
             _check(lib.sb200_forward_wait(_vp(ws.sync)), "sb200_forward_wait")
-            R = int(ws.count[0])
+            R, R_arg = int(ws.count[0]), cap   # the backward locates the hit masks from the value the forward was given
             if R > cap:   # outgrown: only the first `cap` pairs were binned -- size up and run again
                 ws.grow_pairs(R)
-                R = two_stage()
+                R = R_arg = two_stage()
         last_counters.update(P=P, R=R, W=W, H=H)
         ctx.empty = False
         ctx.raster_settings = rs
         ctx.P = P
-        ctx.num_rendered = R
+        ctx.num_rendered = R_arg
         ctx.sh_degree = int(rs.sh_degree)
         ctx.lease = lease   # geometry / image workspaces and the sorted id list live in the leased workspace
         ctx.save_for_backward(means3D, tm_c if ctx.use_pre else scales_c, rot_c, radii, color, others,

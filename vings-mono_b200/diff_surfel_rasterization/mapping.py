@@ -74,7 +74,7 @@ class RasterWorkspace:
         self.image = u8(lib.sb200_image_bytes(W, H))
         self.loss_ws = u8(lib.sb200_map_loss_bytes(W, H))
         self.binning = u8(0)
-        self.point_list = torch.empty(0, dtype=torch.int32, device=device)
+        self.point_list = torch.empty(0, dtype=torch.uint8, device=device)   # sorted ids + hit masks
         self.pair_capacity = 0   # pairs the binning scratch and point_list hold
         self._pending = None     # capacity of an unconfirmed forward_async
         # hand-off state of the sync-free forward, owned by THIS workspace: a pinned landing pad for the pair count
@@ -148,7 +148,7 @@ class RasterWorkspace:
         The first call (no scratch yet) falls back to the synchronising ``forward``."""
         lib = _load()
         P, W, H, dev = self.P, self.W, self.H, self.device
-        cap = min(self.point_list.numel(), self.pair_capacity)
+        cap = self.pair_capacity
         if cap < 1:
             self._pending = None
             return self.forward(means3D, scales, rotations, opacities, colors, bg, viewmatrix, projmatrix)
@@ -180,20 +180,16 @@ class RasterWorkspace:
 
     def _grow_pairs(self, R):
         lib = _load()
-        need = lib.sb200_binning_bytes(R)
-        if self.binning.numel() < need:
-            self.binning = torch.empty(int(need * 1.25) + 4096, dtype=torch.uint8, device=self.device)
-        if self.point_list.numel() < R:
-            self.point_list = torch.empty(int(R * 1.25) + 1024, dtype=torch.int32, device=self.device)
-        # largest pair count both buffers hold (sb200_binning_bytes is monotone: bisect)
-        lo, hi = 0, self.point_list.numel()
-        while lo < hi:
-            mid = (lo + hi + 1) // 2
-            if lib.sb200_binning_bytes(mid) <= self.binning.numel():
-                lo = mid
-            else:
-                hi = mid - 1
-        self.pair_capacity = lo
+        want = int(R * 1.25) + 4096
+        self.binning = torch.empty(lib.sb200_binning_bytes(want), dtype=torch.uint8, device=self.device)
+        self.point_list = torch.empty(lib.sb200_pair_list_bytes(want, self.W, self.H), dtype=torch.uint8,
+                                      device=self.device)
+        self.pair_capacity = want
+
+    def sorted_ids(self, R=None):
+        """The first R entries of the pair list: surfel ids sorted by (tile, depth)."""
+        R = self.R_seen if R is None else R
+        return self.point_list[:4 * R].view(torch.int32)
 
     def backward(self, d_color, d_allmap, means3D, scales, rotations, bg, viewmatrix, projmatrix, tanfovx, tanfovy,
                  pixel_mask=None):
@@ -237,3 +233,68 @@ def surfel_update(mode, params, exp_avg, exp_avg_sq, lr, ws, stable_mask, local_
                                    int(kf), _ptr(fused) if fused is not None else _vp(None), lr_arr,
                                    float(betas[0]), float(betas[1]), float(eps), _stream(params[0].device)),
            "sb200_surfel_update")
+
+
+class PeerExchange:
+    """The multi-GPU exchange of one optimizer step as three kernels over NVLink peer memory (csrc/dp_exchange.cu):
+    every rank stages the rows of the surfels ITS view saw, reduces the slice of surfels it owns by loading its
+    peers' rows, and every rank then applies bookkeeping + Adam from the owners' result rows.  PyTorch's symmetric
+    memory provides the peer-mapped allocation and the barrier between the kernels; nothing else of it is used."""
+
+    def __init__(self, capacity, group, device):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm_mem
+        lib = _load()
+        self.group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+        if self.world > 16:
+            raise RuntimeError("PeerExchange supports up to 16 ranks")
+        self.capacity, self.device = int(capacity), device
+        N = self.world
+        self.slice_cap = ((self.capacity + N - 1) // N + 255) // 256 * 256
+        a256 = lambda n: (n + 255) // 256 * 256
+        self.off_stage = 0
+        self.off_vis = self.off_stage + lib.sb200_dp_stage_bytes(self.capacity)
+        self.off_out = self.off_vis + a256(self.capacity)
+        self.off_upd = self.off_out + lib.sb200_dp_out_bytes(self.slice_cap)
+        total = self.off_upd + a256(self.slice_cap)
+        self.buf = symm_mem.empty(total, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, self.group)
+        bases = [int(p) for p in self.hdl.buffer_ptrs]
+        if len(bases) != N or not all(bases):
+            raise RuntimeError("symmetric memory rendezvous returned no peer pointers")
+        arr = lambda off: (ctypes.c_void_p * N)(*[b + off for b in bases])
+        self.peer_stage, self.peer_vis = arr(self.off_stage), arr(self.off_vis)
+        self.peer_out, self.peer_upd = arr(self.off_out), arr(self.off_upd)
+        self.local = bases[self.rank]
+        torch.cuda.synchronize(device)
+        self.hdl.barrier(channel=0)   # every rank has zeroed its buffer before anyone reads it
+
+    def slice_rows(self, P):
+        """Rows per owner for P surfels (the same on every rank: multiple of 256, P <= slice * world)."""
+        return ((P + self.world - 1) // self.world + 255) // 256 * 256
+
+    def step(self, ws, params, exp_avg, exp_avg_sq, lr, stable_mask, local_scores, global_scores, kf_max_scores, kf_id,
+             kf_ids, betas=(0.9, 0.999), eps=1e-15):
+        lib = _load()
+        P, dev = params[0].shape[0], self.device
+        if P > self.capacity:
+            raise RuntimeError("PeerExchange: %d surfels exceed the capacity %d" % (P, self.capacity))
+        st = _stream(dev)
+        S = self.slice_rows(P)
+        lo, hi = min(P, self.rank * S), min(P, (self.rank + 1) * S)
+        _check(lib.sb200_dp_stage(P, _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
+                                  _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
+                                  _ptr(params[4]), _vp(self.local + self.off_stage), _vp(self.local + self.off_vis), st),
+               "sb200_dp_stage")
+        self.hdl.barrier(channel=0)
+        kf_arr = (ctypes.c_int64 * self.world)(*[int(k) for k in kf_ids])
+        _check(lib.sb200_dp_reduce(lo, hi, self.world, self.peer_stage, self.peer_vis, kf_arr, _ptr(global_scores),
+                                   _vp(self.local + self.off_out), _vp(self.local + self.off_upd), st), "sb200_dp_reduce")
+        self.hdl.barrier(channel=1)
+        lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
+        _check(lib.sb200_dp_post(P, S, self.world, self.peer_out, self.peer_upd, _ptr_array(params), _ptr_array(exp_avg),
+                                 _ptr_array(exp_avg_sq), _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores),
+                                 _ptr(kf_max_scores), _ptr(kf_id), lr_arr, float(betas[0]), float(betas[1]), float(eps),
+                                 st), "sb200_dp_post")

@@ -11,14 +11,20 @@ same step can be driven through this package *or* through the unmodified referen
     optimizer.step  gaussian_base.py:400-403   SparseGaussianAdam.step(radii > 0, P)
 
 Multi-GPU (new; the reference has no multi-GPU code): the views of the keyframe
-window are partitioned over the ranks, surfels are replicated, and one NCCL all-reduce of a fused
-``[P,16]`` fp32 buffer (13 parameter-gradient columns + 2 score columns + 1 visibility column)
-precedes the identical Adam step on every rank.
+window are partitioned over the ranks, surfels are replicated.  Every optimizer step takes ONE view per rank:
+per surfel the per-view-weighted gradients are summed, the score bookkeeping (add_records) is applied for every
+view IN RANK ORDER -- so every replica ends up with the bits a single process taking the same views in that order
+would have, `_globalkf_id` included -- and the identical masked Adam step follows.  The fused path exchanges only
+the rows of surfels a view saw, through kernels over NVLink peer memory (``mapping.PeerExchange``:
+stage -> reduce-scatter by peer loads -> all-gather fused into the update); where peer memory is unavailable it
+falls back to NCCL (a dense ``[16,P]`` sum all-reduce plus a max all-reduce for the order-dependent bookkeeping).
 
 PyTorch here is plumbing (parameters, autograd graph, loss glue); every rasterizer stage and the Adam
 update run in the module handed in.
 """
 import math
+import os
+import sys
 
 import torch
 import torch.nn.functional as F
@@ -93,7 +99,8 @@ def depth_propagate_normal(depth, fx, fy, cx, cy):
 class SurfelMapper:
     """Surfel parameters + optimizer + the per-view training iteration, for a given rasterizer module."""
 
-    def __init__(self, module, scene, device, supervision="rgb+depth", world_size=1, process_group=None, fused=None):
+    def __init__(self, module, scene, device, supervision="rgb+depth", world_size=1, process_group=None, fused=None,
+                 rank=0, exchange=None):
         """fused: run the per-view iteration through the module's fused mapping blocks (``module.mapping``:
         activate / RasterWorkspace / map_loss / surfel_update, SURVEY.md section 8f N1+N2) instead of torch
         autograd + torch loss.  Default: on when the module has them (the reference build has not)."""
@@ -107,7 +114,11 @@ class SurfelMapper:
         self.fx = self.fy = 0.8 * self.W
         self.cx, self.cy = self.W / 2.0, self.H / 2.0
         self.world_size = world_size
+        self.rank = rank
         self.pg = process_group
+        # fused multi-GPU exchange: "p2p" (kernels over NVLink peer memory) or "nccl"; default p2p with a loud fallback
+        self.exchange = exchange or os.environ.get("SB200_DP_EXCHANGE", "p2p")
+        self._dpx = None
         self.bg = torch.zeros(3, device=device)
         self.window = _ssim_window(3, device)
         self.set_surfels(scene)
@@ -179,18 +190,48 @@ class SurfelMapper:
                                 _globalkf_max_scores=st.view("_globalkf_max_scores").reshape(P)))
 
     def _bind_dp(self):
-        if self.world_size > 1:
-            # fused gradient buffer: parameter .grad tensors are column blocks of one allocation so that a
-            # single NCCL all-reduce moves gradients, scores and visibility
-            P, dev = self.P, self.device
-            self._fused = torch.zeros(16 * P, device=dev)
-            self._grad_views, off = {}, 0
-            for k in GROUPS:
-                n = GROUP_COLS[k] * P
-                self._grad_views[k] = self._fused[off:off + n].view(P, GROUP_COLS[k])
-                off += n
-            self._score_view = self._fused[off:off + 2 * P].view(P, 2)
-            self._vis_view = self._fused[off + 2 * P:off + 3 * P]
+        if self.world_size <= 1:
+            return
+        P, dev = self.P, self.device
+        if self.fused and self.exchange == "p2p":
+            cap = self.store.capacity
+            if self._dpx is None or self._dpx.capacity < cap:
+                try:
+                    self._dpx = self.mod.mapping.PeerExchange(cap, self.pg, dev)
+                except Exception as e:  # noqa: BLE001 -- no peer memory on this box: say so and use NCCL
+                    print("[surfel_b200] peer-memory exchange unavailable (%r): falling back to NCCL all-reduce" % (e,),
+                          file=sys.stderr, flush=True)
+                    self.exchange = "nccl"
+            if self.exchange == "p2p":
+                return
+        # NCCL / gloo paths: parameter .grad tensors are column blocks of one allocation so that a single all-reduce
+        # moves gradients, the score sum and the visibility count
+        self._fused = torch.zeros(16 * P, device=dev)
+        self._grad_views, off = {}, 0
+        for k in GROUPS:
+            n = GROUP_COLS[k] * P
+            self._grad_views[k] = self._fused[off:off + n].view(P, GROUP_COLS[k])
+            off += n
+        self._score_view = self._fused[off:off + 2 * P].view(P, 2)
+        self._vis_view = self._fused[off + 2 * P:off + 3 * P]
+
+    def parallelism(self):
+        if self.world_size <= 1:
+            return "single GPU"
+        how = ("kernels over NVLink peer memory: stage rows of visible surfels, reduce-scatter by peer loads, "
+               "all-gather fused into the Adam update" if (self.fused and self.exchange == "p2p")
+               else "dense [16,P] sum all-reduce + [2,P] max all-reduce (NCCL)" if self.fused
+               else "torch: fused [16,P] all-reduce + all-gather of the view scores")
+        return "window views partitioned over %d ranks, surfels replicated; exchange = %s" % (self.world_size, how)
+
+    def _all_kf_ids(self, kf_id, kf_ids):
+        """The keyframe ids of every rank's view this step, in rank order (host ints)."""
+        if kf_ids is not None:
+            assert len(kf_ids) == self.world_size and int(kf_ids[self.rank]) == int(kf_id)
+            return [int(k) for k in kf_ids]
+        out = [None] * self.world_size   # slow path (host round trip): callers that know the schedule pass kf_ids
+        torch.distributed.all_gather_object(out, int(kf_id), group=self.pg)
+        return out
 
     # ---- churn: gaussian_model.py:92-161 (add_new_frame), gaussian_base.py:74-112 ----
     @torch.no_grad()
@@ -270,11 +311,12 @@ class SurfelMapper:
         return rets
 
     # ---- gaussian_base.py:353-404, one iteration ----
-    def train_view(self, view, gt, kf_id=0):
+    def train_view(self, view, gt, kf_id=0, kf_ids=None):
         """render -> loss -> backward -> score bookkeeping -> weighting_grad -> masked Adam.  Returns the loss
-        tensor (device).  With world_size > 1 every rank calls this with its own view of the window."""
+        tensor (device).  With world_size > 1 every rank calls this with its own view of the window; kf_ids = the
+        keyframe ids of ALL ranks' views of this step in rank order (gathered if not given)."""
         if self.fused:
-            return self._train_view_fused(view, gt, kf_id)
+            return self._train_view_fused(view, gt, kf_id, kf_ids)
         dp = self.world_size > 1
         if dp:
             self._fused.zero_()
@@ -291,8 +333,12 @@ class SurfelMapper:
             self._score_view.copy_(cur)
             self._vis_view.copy_(radii > 0)
             torch.distributed.all_reduce(self._fused, group=self.pg)
-            cur = self._score_view
-            self._add_records(cur, kf_id)
+            # add_records is order dependent (max of the second score, first arg-max of the first): every rank applies
+            # it for every view in rank order, so the replicas -- _globalkf_id included -- stay identical
+            curs = [torch.empty_like(cur) for _ in range(self.world_size)]
+            torch.distributed.all_gather(curs, cur.contiguous(), group=self.pg)
+            for q, kf in enumerate(self._all_kf_ids(kf_id, kf_ids)):
+                self._add_records(curs[q], kf)
             visible = self._vis_view > 0
         else:
             self._add_records(cur, kf_id)
@@ -307,7 +353,7 @@ class SurfelMapper:
         return total_loss.detach()
 
     @torch.no_grad()
-    def _train_view_fused(self, view, gt, kf_id):
+    def _train_view_fused(self, view, gt, kf_id, kf_ids=None):
         """The same iteration in 22 launches of the library: activate -> rasterizer forward -> fused loss ->
         rasterizer backward -> one per-surfel update kernel (two around the all-reduce with world_size > 1)."""
         mp, ws = self.mod.mapping, self._ws
@@ -331,14 +377,36 @@ class SurfelMapper:
                 break
             raster = ws.forward
         book = (self._stable_mask, self._local_scores, self._global_scores, self._globalkf_max_scores, self._globalkf_id)
-        if self.world_size > 1:
-            mp.surfel_update(mp.UPDATE_DP_PRE, prm, m, v, lr, ws, *book, kf_id, fused=self._fused, eps=eps)
-            torch.distributed.all_reduce(self._fused, group=self.pg)
-            mp.surfel_update(mp.UPDATE_DP_POST, prm, m, v, lr, ws, *book, kf_id, fused=self._fused, eps=eps)
+        if self.world_size > 1 and self.exchange == "p2p":
+            self._dpx.step(ws, prm, m, v, lr, *book, self._all_kf_ids(kf_id, kf_ids), eps=eps)
+        elif self.world_size > 1:
+            self._nccl_step(mp, ws, prm, m, v, lr, book, self._all_kf_ids(kf_id, kf_ids), eps)
         else:
             mp.surfel_update(mp.UPDATE_LOCAL, prm, m, v, lr, ws, *book, kf_id, eps=eps)
         self.last_radii = ws.radii
         return loss[0]
+
+    def _nccl_step(self, mp, ws, prm, m, v, lr, book, kf_ids, eps):
+        """Fallback exchange without peer memory: DP_PRE -> dense sum all-reduce -> DP_POST, with add_records' two
+        order-dependent quantities (max of score 1; first arg-max of score 0 and its keyframe id) from one max
+        all-reduce of order-preserving integer keys (non-negative floats compare like their bit patterns)."""
+        dist = torch.distributed
+        N, r, P = self.world_size, self.rank, self.P
+        mp.surfel_update(mp.UPDATE_DP_PRE, prm, m, v, lr, ws, *book, kf_ids[r], fused=self._fused, eps=eps)
+        cur = ws.scores
+        keys = torch.stack(((cur[:, 0].contiguous().view(torch.int32).to(torch.int64) << 32) | (N - 1 - r),
+                            cur[:, 1].contiguous().view(torch.int32).to(torch.int64)))
+        dist.all_reduce(self._fused, group=self.pg)
+        dist.all_reduce(keys, op=dist.ReduceOp.MAX, group=self.pg)
+        self._score_view[:, 1] = (keys[1] & 0xffffffff).to(torch.int32).view(torch.float32)   # max, not sum
+        kfm0, kid0 = self._globalkf_max_scores.clone(), self._globalkf_id.clone()
+        mp.surfel_update(mp.UPDATE_DP_POST, prm, m, v, lr, ws, *book, kf_ids[r], fused=self._fused, eps=eps)
+        s0_max = (keys[0] >> 32).to(torch.int32).view(torch.float32)
+        arg = (N - 1) - (keys[0] & 0xffffffff)                 # lowest rank among equal maxima = first in rank order
+        kf_arg = torch.tensor(kf_ids, dtype=torch.int64, device=self.device)[arg]
+        replace = kfm0 < s0_max
+        self._globalkf_max_scores.copy_(torch.where(replace, s0_max, kfm0))
+        self._globalkf_id.copy_(torch.where(replace, kf_arg, kid0))
 
     def _add_records(self, cur, kf_id):
         """gaussian_model.py:163-168 and gaussian_base.py:388-392"""
