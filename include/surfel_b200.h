@@ -201,6 +201,28 @@ int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp
                         int64_t* kf_id, int64_t kf, float* fused, const float* lr, float b1, float b2, float eps,
                         void* stream);
 
+/* sb200_backward_update: sb200_backward and sb200_surfel_update as ONE call for the fused mapping step - the backward
+ * blend, then a single per-surfel pass that leaves a surfel the view did not see (radii <= 0) untouched and takes a
+ * visible one from its accumulation record through the backward preprocess (cuda_rasterizer/backward.cu:849-1045), the
+ * activations' backward, add_records, weighting_grad and the masked Adam step without the dense [P,*] gradient arrays
+ * in between (72 B written and ~60 B read back per surfel by the two-call form).
+ *   means3D / scales / rotations: the rasterizer inputs of this view (activated); params: the five RAW parameter arrays
+ *   (params[0] is means3D); the rest as sb200_surfel_update.
+ *   mode 0: single-GPU update (SB200_UPDATE_LOCAL semantics).
+ *   mode 1: multi-GPU stage - writes what sb200_dp_stage writes (stage rows of visible surfels, vis bytes) and updates
+ *           nothing; exp_avg .. lr may be NULL.
+ *   R < 0 (test hook): skip the blend, grad_ws already holds the view's accumulation records. */
+int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                          const float* means3D, const float* scales, const float* rotations,
+                          const float* viewmatrix, const float* projmatrix, const int* radii,
+                          const void* geom_ws, const uint32_t* point_list, const void* image_ws,
+                          const float* out_color, const float* out_others, const float* dL_dout_color,
+                          const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws, int mode,
+                          float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+                          const uint8_t* stable_mask, float* local_scores, float* global_scores,
+                          float* kf_max_scores, int64_t* kf_id, int64_t kf, const float* lr, float b1,
+                          float b2, float eps, float* stage, uint8_t* vis, void* stream);
+
 /* ---- multi-GPU exchange of the mapping step over NVLink peer memory ----------------------
  * One optimizer step takes ONE view per rank (window views partitioned over the GPUs of a box, surfels replicated).
  * The three calls below replace "sb200_surfel_update(DP_PRE) -> NCCL all-reduce of [16,P] -> sb200_surfel_update(

@@ -111,73 +111,3 @@ def test_block_cull_never_drops_a_passing_pixel(cfg, P):
     # the test is not vacuous: it skips most far blocks, and few all-rejecting blocks are still visited
     assert culled_blocks > 0.5 * total, (culled_blocks, total)
     assert kept_blocks < 0.2 * total, (kept_blocks, total)
-
-
-def dop_bounds(Tu, Tv, Tw, xy, tau):
-    """surfel_math.cuh::sb_cull_data, the 8 int16 bounds (min, max) along x, y, x+y, x-y -- same float32 operations"""
-    BIG = f32(1e30)
-    with np.errstate(all="ignore"):
-        dist = (tau * (Tw[:, 0] * Tw[:, 0] + Tw[:, 1] * Tw[:, 1]) - Tw[:, 2] * Tw[:, 2]).astype(f32)
-        inv = (f32(1.0) / dist).astype(f32)
-        fx, fz = (tau * inv).astype(f32), (-inv).astype(f32)
-        Td = [Tu, Tv, (Tu + Tv).astype(f32), (Tu - Tv).astype(f32)]
-        cc, hh = [], []
-        for T in Td:
-            c_ = (fx * (T[:, 0] * Tw[:, 0] + T[:, 1] * Tw[:, 1]) + fz * T[:, 2] * Tw[:, 2]).astype(f32)
-            h_ = (c_ * c_ - (fx * (T[:, 0] * T[:, 0] + T[:, 1] * T[:, 1]) + fz * T[:, 2] * T[:, 2])).astype(f32)
-            cc.append(c_)
-            hh.append(h_)
-        ok = (dist < 0) & np.all([h >= 0 for h in hh], axis=0)
-        rd = (np.sqrt(f32(0.5) * tau) + f32(0.5)).astype(f32)
-        ctr = [xy[:, 0], xy[:, 1], (xy[:, 0] + xy[:, 1]).astype(f32), (xy[:, 0] - xy[:, 1]).astype(f32)]
-        out = np.zeros((len(tau), 8), np.int64)
-        for k in range(4):
-            e = (np.sqrt(np.maximum(hh[k], 0)) + f32(1.0 if k < 2 else 2.0) + f32(1e-3) * np.abs(cc[k])).astype(f32)
-            lo = np.where(ok, cc[k] - e, -BIG).astype(f32)
-            hi = np.where(ok, cc[k] + e, BIG).astype(f32)
-            r = rd if k < 2 else (f32(1.41421357) * rd + f32(1e-3) * (np.abs(xy[:, 0]) + np.abs(xy[:, 1]))).astype(f32)
-            lo, hi = np.minimum(lo, ctr[k] - r), np.maximum(hi, ctr[k] + r)
-            nan = ~(lo <= hi)
-            lo, hi = np.where(nan, -BIG, lo), np.where(nan, BIG, hi)
-            out[:, 2 * k] = np.clip(np.floor(lo.astype(np.float64)), -32768, 32767)
-            out[:, 2 * k + 1] = np.clip(np.ceil(hi.astype(np.float64)), -32768, 32767)
-        return out
-
-
-@pytest.mark.parametrize("cfg,P", [("C1", 4000), ("C3", 4000), ("C2", 4000), ("C4", 4000)])
-def test_direction_bounds_never_drop_a_passing_pixel(cfg, P):
-    """The forward blend's first-level cull: a block whose x / y / x+y / x-y ranges miss the record's bounds is
-    skipped without any per-pixel test, so no pixel of it may pass the lane-level test."""
-    scene, views = synthetic.make_scene(cfg, P=P, W=320, H=240)
-    inp = synthetic.view_inputs(scene, views[-1])
-    pre = emu.preprocess(inp["means3D"], inp["scales"], inp["rotations"], inp["opacities"], inp["viewmatrix"],
-                         inp["projmatrix"], inp["W"], inp["H"])
-    vis = pre["visible"].numpy()
-    T = pre["T"].numpy().astype(f32)[vis]
-    xy = pre["means2D"].numpy().astype(f32)[vis]
-    opa = inp["opacities"].numpy().astype(f32).reshape(-1)[vis]
-    A, B, C, tau = cull_data(T[:, 0], T[:, 1], T[:, 2], xy, opa)
-    dop = dop_bounds(T[:, 0], T[:, 1], T[:, 2], xy, tau)
-    n = len(xy)
-    assert n > 300
-    lx, ly = np.arange(8, dtype=f32), np.arange(4, dtype=f32)
-    cbx, cby = np.floor(xy[:, 0] / 8).astype(np.int64), np.floor(xy[:, 1] / 4).astype(np.int64)
-    rej_box = rej_dop = passing_blocks = 0
-    for ox in range(-8, 9):
-        for oy in range(-16, 17):
-            bx0, by0 = (cbx + ox) * 8, (cby + oy) * 4
-            box_ov = (dop[:, 0] <= bx0 + 7) & (dop[:, 1] >= bx0) & (dop[:, 2] <= by0 + 3) & (dop[:, 3] >= by0)
-            dia_ov = ((dop[:, 4] <= bx0 + by0 + 10) & (dop[:, 5] >= bx0 + by0) &
-                      (dop[:, 6] <= bx0 - by0 + 7) & (dop[:, 7] >= bx0 - by0 - 3))
-            px = (bx0[:, None] + np.tile(lx, 4)[None, :]).astype(f32)
-            py = (by0[:, None] + np.repeat(ly, 8)[None, :]).astype(f32)
-            some_pixel_passes = ~lane_culled(A, B, C, tau, xy, px, py).all(1)
-            bad = some_pixel_passes & ~(box_ov & dia_ov)
-            assert not bad.any(), (cfg, ox, oy, int(bad.sum()))
-            rej_box += int((~box_ov).sum())
-            rej_dop += int((~(box_ov & dia_ov)).sum())
-            passing_blocks += int(some_pixel_passes.sum())
-    total = n * 17 * 33
-    # not vacuous: the diagonal slabs reject blocks the axis-aligned box lets through
-    assert rej_dop > rej_box and passing_blocks > 0, (rej_box, rej_dop, passing_blocks, total)
-    print("%s: of %d blocks the box rejects %d, box+diagonals %d; %d contain a passing pixel" % (cfg, total, rej_box, rej_dop, passing_blocks))

@@ -381,3 +381,72 @@ def test_peer_exchange_kernels_equal_the_batched_step_on_one_device():
         kid = torch.where(rep, torch.full_like(kid, kf_ids[q]), kid)
     assert torch.equal(ba[2], kfm) and torch.equal(ba[3], kid) and torch.equal(ba[0][:, 1], loc[:, 1])
     assert torch.allclose(ba[0][:, 0], loc[:, 0], rtol=1e-6, atol=0) and torch.allclose(ba[1], glo, rtol=1e-6, atol=0)
+
+
+@pytest.mark.gpu
+def test_backward_update_equals_backward_then_update():
+    """sb200_backward_update (backward blend + ONE per-surfel pass over the visible surfels) against the two-call form
+    sb200_backward -> sb200_surfel_update(LOCAL) / sb200_dp_stage it replaces in the fused mapper, on the SAME
+    accumulation records (R < 0 test hook: two backward blends would differ by atomic-order jitter).  What is left is
+    fp32 contraction of the same backward-preprocess expressions inlined into another kernel: a few ulp."""
+    mine = util.load_mine()
+    mp, lib = mine.mapping, mine._load()
+    scene, views = synthetic.make_scene("C3", P=30000, W=160, H=96)
+    dev = torch.device("cuda")
+    m = mapper_step.SurfelMapper(mine, scene, dev, supervision="rgb+depth+normal+dist", fused=True)
+    gts = [{k: t.cuda() for k, t in synthetic.make_gt(scene, v, i).items()} for i, v in enumerate(views[:2])]
+    vds = [mapper_step.view_to_device(v, dev) for v in views[:2]]
+    m.train_view(vds[1], gts[1], kf_id=4)   # non-trivial moments and scores (through backward_update itself)
+    assert float(m.optimizer.state[m._xyz]["exp_avg"].abs().sum()) > 0
+    P, ws = m.P, m._ws
+    prm = [getattr(m, k).data for k in mapper_step.GROUPS]
+    lr = [mapper_step.LR[k] for k in mapper_step.GROUPS]
+    g = torch.Generator(device="cpu").manual_seed(4)
+    stable = (torch.rand(P, generator=g) < 0.1).cuda()
+    opac, scales, rot = mp.activate(prm[2], prm[3], prm[4])
+    vd, gt = vds[0], gts[0]
+    ws.forward(prm[0], scales, rot, opac, prm[1], m.bg, vd["viewmatrix"], vd["projmatrix"])
+    loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gt["rgb"], gt["depth"], gt["depth_cov"], vd["w2c"], m.cx,
+                                          m.cy, m.fx, m.fy, m.weights, ws=ws.loss_ws, out=ws.loss_out)
+    ws.backward(d_color, d_allmap, prm[0], scales, rot, m.bg, vd["viewmatrix"], vd["projmatrix"], vd["tanfovx"], vd["tanfovy"])
+
+    def state():
+        st = [m.optimizer.state[getattr(m, k)] for k in mapper_step.GROUPS]
+        return ([p.clone() for p in prm], [x["exp_avg"].clone() for x in st], [x["exp_avg_sq"].clone() for x in st],
+                [m._local_scores.clone(), m._global_scores.clone(), m._globalkf_max_scores.clone(), m._globalkf_id.clone()])
+
+    pa, ma, va, ba = state()
+    mp.surfel_update(mp.UPDATE_LOCAL, pa, ma, va, lr, ws, stable, *ba, 7)
+    pb, mb, vb, bb = state()
+    mp.backward_update(ws, 0, d_color, d_allmap, prm[0], scales, rot, m.bg, vd["viewmatrix"], vd["projmatrix"],
+                       vd["tanfovx"], vd["tanfovy"], pb, mb, vb, lr, stable, *bb, 7, reuse_records=True)
+    torch.cuda.synchronize()
+    for x, y in zip(ba, bb):      # the scores come straight out of the records: bookkeeping is exact
+        assert torch.equal(x, y)
+    for k, x, y in zip(mapper_step.GROUPS, ma + va, mb + vb):
+        assert util.rel_err(y, x) < 1e-6, (k, util.rel_err(y, x))
+    for k, x, y, p0 in zip(mapper_step.GROUPS, pa, pb, prm):
+        assert float((x - y).abs().max()) <= 1e-4 * util.ADAM_RATIO_MAX * mapper_step.LR[k] + 2.5e-7 * float(x.abs().max()), k
+        assert not torch.equal(x, p0) and torch.equal(y[stable], p0[stable])
+        vis = ws.radii > 0
+        assert torch.equal(y[~vis], p0[~vis])
+    # mode 1: the multi-GPU stage rows, against sb200_dp_stage on the dense outputs
+    vp = ctypes.c_void_p
+    st_ = vp(torch.cuda.current_stream().cuda_stream)
+    stage_a = torch.zeros(lib.sb200_dp_stage_bytes(P) // 4, device=dev)
+    stage_b = torch.zeros_like(stage_a)
+    vis_a, vis_b = torch.full((P,), 7, dtype=torch.uint8, device=dev), torch.full((P,), 7, dtype=torch.uint8, device=dev)
+    assert lib.sb200_dp_stage(P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()), vp(ws.d_opacity.data_ptr()),
+                              vp(ws.d_scales.data_ptr()), vp(ws.d_rot.data_ptr()), vp(ws.scores.data_ptr()),
+                              vp(ws.radii.data_ptr()), vp(prm[2].data_ptr()), vp(prm[3].data_ptr()),
+                              vp(prm[4].data_ptr()), vp(stage_a.data_ptr()), vp(vis_a.data_ptr()), st_) == 0
+    before = state()
+    mp.backward_update(ws, 1, d_color, d_allmap, prm[0], scales, rot, m.bg, vd["viewmatrix"], vd["projmatrix"],
+                       vd["tanfovx"], vd["tanfovy"], prm, None, None, lr, None, None, None, None, None, 7,
+                       stage=stage_b.data_ptr(), vis=vis_b.data_ptr(), reuse_records=True)
+    torch.cuda.synchronize()
+    assert torch.equal(vis_a, vis_b) and torch.equal(vis_a.bool(), ws.radii > 0)
+    assert util.rel_err(stage_b, stage_a) < 1e-6
+    assert torch.equal(stage_b.view(P, 16)[:, 13:15][vis_a.bool()], ws.scores[vis_a.bool()])
+    for x, y in zip(before[0] + before[1] + before[2] + before[3], state()[0] + state()[1] + state()[2] + state()[3]):
+        assert torch.equal(x, y)   # mode 1 updates nothing

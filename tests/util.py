@@ -208,7 +208,7 @@ def mine_intermediates(mine, inp):
                 means2D=np.stack([rec[:, 3], rec[:, 7]], -1),
                 transMat=np.concatenate([rec[:, 12:15], rec[:, 16:19], rec[:, 20:23]], -1),
                 normal_opacity=np.concatenate([rec[:, 24:27], rec[:, 15:16]], -1),
-                cull_tau=rec[:, 11], dop=rec[:, 28:32].copy().view(np.int16).reshape(P, 8),
+                cull_tau=rec[:, 11], bbox=rec[:, 28:32],
                 keys=keys_sorted, point_list=pl, ranges=ranges,
                 final_T=fb(im, io[1], 12 * N, np.float32).reshape(3, N),
                 n_contrib=fb(im, io[2], 8 * N, np.uint32).reshape(2, N))

@@ -23,7 +23,7 @@ worst = torch.argsort(d[:, 0], descending=True)[:6]
 for i in worst.tolist():
     print(i, "score mine/ref", om["d_scores"][i].tolist(), orf["d_scores"][i].tolist(), "radius", int(mi["radii"][i]),
           "rect", mi["rect"][i].tolist(), "xy", mi["means2D"][i].tolist(), "tau", float(mi["cull_tau"][i]),
-          "dop", mi["dop"][i].tolist(), "opa", float(inp["opacities"][i]))
+          "bbox", mi["bbox"][i].tolist(), "opa", float(inp["opacities"][i]))
 if "--emu" in sys.argv:
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import surfel_emulation as emu

@@ -62,7 +62,9 @@ def build(force=False, verbose=False):
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
     if force or _stale(OUT, objs):
-        subprocess.run(["nvcc", "-shared", "-o", OUT] + objs + ["-lcudart"], check=True)
+        # (the arch is repeated at the link step: without it nvcc compiles its link stub for its default sm_52)
+        subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT] + objs + ["-lcudart"],
+                       check=True)
     return OUT
 
 

@@ -50,13 +50,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     const bool inside = px < (uint32_t)W && py < (uint32_t)H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
-    // the block's pixel-centre ranges along x, y, x+y, x-y, saturated like the records' int16 bounds
-    const int kx0 = min((int)wx0, 32767), kx1 = min((int)wx0 + 7, 32767), ky0 = min((int)wy0, 32767), ky1 = min((int)wy0 + 3, 32767);
-    const int ks0 = min((int)(wx0 + wy0), 32767), ks1 = min((int)(wx0 + wy0) + 10, 32767);
-    const int kd0 = max(min((int)wx0 - (int)wy0 - 3, 32767), -32768), kd1 = max(min((int)wx0 - (int)wy0 + 7, 32767), -32768);
-#ifdef SB_BLOCK_CULL
     const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
-#endif
     bool done = !inside;
 
     const uint2 range = ranges[tile];
@@ -115,16 +109,12 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
             // (measured and dropped, round 2, tools/time_stages.py A/B on C2-C5: shrinking the block to the bounding box of
             // its still-live pixels is neutral; a four-corner "footprint contains the whole block" test that skips phase 1
             // costs 12-14 % at C4/C5 -- the synthetic clouds' randomly oriented surfels project to thin ellipses that
-            // rarely contain an 8x4 block)
+            // rarely contain an 8x4 block; bounds along the two diagonals as well (x+y, x-y: conservative, 16 % fewer
+            // box-passing blocks on CPU) cost 2-3 % at C4/C5 -- the eight int16 compares per surfel outweigh them)
             bool ov = false;
             if (c + lane < cnt) {
-                // footprint bounds along x, y and the two diagonals against the block's ranges (8 int16 per record)
-                const float4 bf = sq[c + lane][SB_REC_BBOX];
-                const int b0 = __float_as_int(bf.x), b1 = __float_as_int(bf.y), b2 = __float_as_int(bf.z), b3 = __float_as_int(bf.w);
-                ov = (int)(short)b0 <= kx1 && (b0 >> 16) >= kx0 && (int)(short)b1 <= ky1 && (b1 >> 16) >= ky0;
-#ifndef FB_NO_DIAG
-                ov = ov && (int)(short)b2 <= ks1 && (b2 >> 16) >= ks0 && (int)(short)b3 <= kd1 && (b3 >> 16) >= kd0;
-#endif
+                const float4 bb = sq[c + lane][SB_REC_BBOX];
+                ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
 #ifdef SB_BLOCK_CULL  // opt-in: measured neutral
                 if (ov) ov = !sb_block_culled(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bx0, bx1, by0, by1);
 #endif

@@ -27,8 +27,7 @@
 //   q4 = (Tv.x, Tv.y, Tv.z, r)
 //   q5 = (Tw.x, Tw.y, Tw.z, g)
 //   q6 = (n.x,  n.y,  n.z,  b)
-//   q7 = 8 x int16: min | max << 16 along x, y, x+y, x-y   pixel-space bounds outside of which the surfel cannot
-//                                      reach alpha >= 1/255 (surfel_math.cuh, SbCull::dop)
+//   q7 = (xmin, xmax, ymin, ymax)      pixel-space box outside of which the surfel cannot reach alpha >= 1/255
 #define SB_REC_F4 8
 #define SB_REC_CULL 0
 #define SB_REC_TU 3

@@ -103,8 +103,7 @@ sb_preprocess_kernel(int P, int W, int H, const float* __restrict__ means3D, con
                     r[4] = make_float4(Tv.x, Tv.y, Tv.z, s_col[3 * threadIdx.x]);
                     r[5] = make_float4(Tw.x, Tw.y, Tw.z, s_col[3 * threadIdx.x + 1]);
                     r[6] = make_float4(normal.x, normal.y, normal.z, s_col[3 * threadIdx.x + 2]);
-                    r[7] = make_float4(__uint_as_float(cull.dop.x), __uint_as_float(cull.dop.y),
-                                       __uint_as_float(cull.dop.z), __uint_as_float(cull.dop.w));
+                    r[7] = cull.bbox;
                 }
             }
         }

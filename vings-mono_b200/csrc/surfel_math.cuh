@@ -199,18 +199,12 @@ __device__ __forceinline__ void sb_get_rect(float2 p, int max_radius, uint2& rec
 //  * rho3d > tau  <=>  p.x^2 + p.y^2 > tau p.z^2 where p = (px Tw - Tu) x (py Tw - Tv) is AFFINE in the
 //    pixel:  p = Tu x Tv + px (Tv x Tw) + py (Tw x Tu).  Re-centred on the surfel's screen centre xy and
 //    with (dx,dy) = xy - pixel:  p = C + A dx + B dy.  Scaled by 1/|C.z| (the test is homogeneous).
-//  * the screen-space bounds of {rho3d <= tau} follow compute_aabb (forward.cu:130-157) with the cutoff
-//    weights (tau, tau, -1), along x, y and the two diagonals; they are united with the low-pass disk
-//    {rho2d <= tau} and padded by a pixel.
+//  * the screen-space box of {rho3d <= tau} follows compute_aabb (forward.cu:130-157) with the cutoff
+//    weights (tau, tau, -1); it is united with the low-pass disk {rho2d <= tau} and padded by a pixel.
 struct SbCull {
     float3 A, B, C;
     float tau;
-    // conservative bounds of the footprint {alpha >= 1/255} in pixel coordinates (pixel centres are integers) along
-    // four directions -- x, y, x+y, x-y -- packed as 8 int16 (mins rounded down, maxes up, saturated):
-    //   .x = xmin | xmax << 16   .y = ymin | ymax << 16   .z = (x+y)min | (x+y)max << 16   .w = (x-y)min | (x-y)max << 16
-    // The two diagonal slabs cut the corners off the axis-aligned box: a thin ellipse lying diagonally fills a small
-    // part of its box, and every 8x4 pixel block in the empty corners would otherwise run the per-pixel conic test.
-    uint4 dop;
+    float4 bbox;  // xmin, xmax, ymin, ymax in pixel coordinates (pixel centres are integers)
 };
 
 __device__ __forceinline__ float3 sb_cross(float3 a, float3 b) {
@@ -232,46 +226,25 @@ __device__ __forceinline__ SbCull sb_cull_data(float3 Tu, float3 Tv, float3 Tw, 
     c.A = make_float3(-a.x * n, -a.y * n, -a.z * n);
     c.B = make_float3(-b.x * n, -b.y * n, -b.z * n);
     c.C = make_float3(C.x * n, C.y * n, C.z * n);
-    // extent of the tau-level conic along x, y, x+y, x-y: compute_aabb's dual-conic formula (forward.cu:130-157) with the
-    // cutoff weights (tau, tau, -1), applied to Tu, Tv, Tu+Tv, Tu-Tv (pixel x = Tu.s / Tw.s is linear in T's first rows)
-    float lo[4] = {-BIG, -BIG, -BIG, -BIG}, hi[4] = {BIG, BIG, BIG, BIG};
+    // box of the tau-level ellipse
+    float xmin = -BIG, xmax = BIG, ymin = -BIG, ymax = BIG;
     float dist = tau * (Tw.x * Tw.x + Tw.y * Tw.y) - Tw.z * Tw.z;
     if (dist < 0.0f) {
         float inv = 1.0f / dist;
         float fx = tau * inv, fz = -inv;
-        const float3 Td[4] = {Tu, Tv, make_float3(Tu.x + Tv.x, Tu.y + Tv.y, Tu.z + Tv.z),
-                              make_float3(Tu.x - Tv.x, Tu.y - Tv.y, Tu.z - Tv.z)};
-        float cc[4], hh[4];
-        bool ok = true;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            cc[k] = fx * (Td[k].x * Tw.x + Td[k].y * Tw.y) + fz * Td[k].z * Tw.z;
-            hh[k] = cc[k] * cc[k] - (fx * (Td[k].x * Td[k].x + Td[k].y * Td[k].y) + fz * Td[k].z * Td[k].z);
-            ok = ok && (hh[k] >= 0.0f);  // false for NaN
-        }
-        if (ok) {
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                // pad: one pixel per coordinate involved + a relative term for the cancellation in cc*cc - (...)
-                float e = sqrtf(hh[k]) + (k < 2 ? 1.0f : 2.0f) + 1e-3f * fabsf(cc[k]);
-                lo[k] = cc[k] - e;
-                hi[k] = cc[k] + e;
-            }
+        float cx = fx * (Tu.x * Tw.x + Tu.y * Tw.y) + fz * Tu.z * Tw.z;
+        float cy = fx * (Tv.x * Tw.x + Tv.y * Tw.y) + fz * Tv.z * Tw.z;
+        float hx = cx * cx - (fx * (Tu.x * Tu.x + Tu.y * Tu.y) + fz * Tu.z * Tu.z);
+        float hy = cy * cy - (fx * (Tv.x * Tv.x + Tv.y * Tv.y) + fz * Tv.z * Tv.z);
+        if (hx >= 0.0f && hy >= 0.0f) {  // false for NaN
+            // pad: one pixel + a relative term for the cancellation in cx*cx - (...)
+            float ex = sqrtf(hx) + 1.0f + 1e-3f * fabsf(cx), ey = sqrtf(hy) + 1.0f + 1e-3f * fabsf(cy);
+            xmin = cx - ex; xmax = cx + ex; ymin = cy - ey; ymax = cy + ey;
         }
     }
     float rd = sqrtf(0.5f * tau) + 0.5f;  // low-pass disk rho2d = 2 |xy - pixel|^2 <= tau
-    const float ctr[4] = {xy.x, xy.y, xy.x + xy.y, xy.x - xy.y};
-    uint32_t w[4];
-#pragma unroll
-    for (int k = 0; k < 4; k++) {
-        const float r = k < 2 ? rd : 1.41421357f * rd + 1e-3f * (fabsf(xy.x) + fabsf(xy.y));
-        float l = fminf(lo[k], ctr[k] - r), h = fmaxf(hi[k], ctr[k] + r);
-        if (!(l <= h)) { l = -BIG; h = BIG; }   // NaN
-        const int li = (int)fmaxf(floorf(l), -32768.0f) < 32767 ? (int)fmaxf(floorf(l), -32768.0f) : 32767;
-        const int hi_ = (int)fminf(ceilf(h), 32767.0f) > -32768 ? (int)fminf(ceilf(h), 32767.0f) : -32768;
-        w[k] = ((uint32_t)li & 0xffffu) | ((uint32_t)hi_ << 16);
-    }
-    c.dop = make_uint4(w[0], w[1], w[2], w[3]);
+    c.bbox = make_float4(fminf(xmin, xy.x - rd), fmaxf(xmax, xy.x + rd), fminf(ymin, xy.y - rd), fmaxf(ymax, xy.y + rd));
+    if (!(c.bbox.x <= c.bbox.y) || !(c.bbox.z <= c.bbox.w)) c.bbox = make_float4(-BIG, BIG, -BIG, BIG);
     return c;
 }
 

@@ -15,7 +15,8 @@
 //   SB_UPD_DP_PRE   activation backward + per-view weighting, written with scores and visibility into the
 //                   fused [16,P] buffer that NCCL reduces;
 //   SB_UPD_DP_POST  bookkeeping + Adam from the reduced buffer.
-#include "common.cuh"
+#include "prebwd_math.cuh"
+#include <string.h>
 #include "../../include/surfel_b200.h"
 
 __global__ void sb_activate_kernel(int P, const float* __restrict__ opacity_raw, const float2* __restrict__ scaling_raw,
@@ -223,6 +224,216 @@ int sb_launch_surfel_update(const SbUpdateArgs& a, cudaStream_t s) {
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
+}
+
+// ---- the backward preprocess and the per-surfel update in ONE pass over the visible surfels (round 2) ----
+// sb_preprocess_backward_kernel writes 72 B of dense gradient rows for EVERY surfel (zeros for the ~60 % a view does
+// not see) only for sb_surfel_update_kernel to read them back: 612 MB of measured DRAM traffic per C2 view against
+// ~240 MB that is compulsory (profiles/traffic.json, round 1: 1.43x and 1.59x the algorithmic bytes).  Here a thread
+// looks at its surfel's radius first and leaves at once if the view did not see it (add_records with zero scores and a
+// masked-out Adam step are the identity); a visible surfel's accumulated record goes through the backward preprocess
+// arithmetic (prebwd_math.cuh), the activations' backward, the bookkeeping and Adam without touching memory in
+// between.  MODE 0: the single-GPU update.  MODE 1: the multi-GPU stage row + visibility byte (dp_exchange.cu).
+struct SbViewUpdateArgs {
+    SbUpdateArgs u;                // params, moments, bookkeeping, lr, betas (gradient pointers unused)
+    const float* means3D; const float* act_scales; const float* act_rot;   // the rasterizer's inputs of this view
+    const float* viewmatrix; const float* projmatrix;
+    const float* grad_acc;         // [P, SB_GRAD_F] the backward blend's accumulation records
+    float* stage; uint8_t* vis;    // MODE 1
+    int Wq, Hq;
+};
+
+template <int MODE>
+__global__ void __launch_bounds__(256) sb_view_update_kernel(SbViewUpdateArgs va) {
+    __shared__ float s_vm[16], s_pm[16];
+    if (threadIdx.x < 16) s_vm[threadIdx.x] = va.viewmatrix[threadIdx.x];
+    else if (threadIdx.x < 32) s_pm[threadIdx.x - 16] = va.projmatrix[threadIdx.x - 16];
+    __syncthreads();
+    const SbUpdateArgs& a = va.u;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.P) return;
+    const bool visible = a.radii[i] > 0;
+    if (MODE == 1) va.vis[i] = visible ? 1 : 0;
+    if (!visible) return;
+    const size_t iz = (size_t)i;
+
+    float acc[SB_GRAD_F];
+    {
+        const float4* ga = reinterpret_cast<const float4*>(va.grad_acc + iz * SB_GRAD_F);
+#pragma unroll
+        for (int k = 0; k < SB_GRAD_F / 4; k++) {
+            const float4 v = ga[k];
+            acc[4 * k] = v.x; acc[4 * k + 1] = v.y; acc[4 * k + 2] = v.z; acc[4 * k + 3] = v.w;
+        }
+    }
+    float3 d_mean3D = {0.f, 0.f, 0.f};
+    float2 d_scale = {0.f, 0.f};
+    float4 d_rot = {0.f, 0.f, 0.f, 0.f};
+    sb_prebwd_surfel<false>(i, va.Wq, va.Hq, va.means3D, (const float2*)va.act_scales, (const float4*)va.act_rot, nullptr,
+                            s_vm, s_pm, acc, d_mean3D, d_scale, d_rot);
+    float g[13] = {d_mean3D.x, d_mean3D.y, d_mean3D.z, acc[15], acc[16], acc[17], acc[14], d_scale.x, d_scale.y,
+                   d_rot.x, d_rot.y, d_rot.z, d_rot.w};
+    const float cur0 = acc[18], cur1 = acc[19];
+
+    // raw opacity / scaling / rotation for the activations' backward; parameters and moments for Adam
+    const bool adam = MODE == 0 && !a.stable[i];
+    float pv[13], mv[13], vv[13];
+#pragma unroll
+    for (int c = 0; c < 7; c++) {
+        const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+        const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+        pv[c] = (adam || c >= 6) ? a.param[grp][e] : 0.f;
+        mv[c] = adam ? a.m[grp][e] : 0.f;
+        vv[c] = adam ? a.v[grp][e] : 0.f;
+    }
+    {
+        const float2 s2 = ((const float2*)a.param[3])[i];
+        const float4 q4 = ((const float4*)a.param[4])[i];
+        float2 ms2 = make_float2(0.f, 0.f), vs2 = ms2;
+        float4 mq4 = make_float4(0.f, 0.f, 0.f, 0.f), vq4 = mq4;
+        if (adam) {
+            ms2 = ((const float2*)a.m[3])[i]; vs2 = ((const float2*)a.v[3])[i];
+            mq4 = ((const float4*)a.m[4])[i]; vq4 = ((const float4*)a.v[4])[i];
+        }
+        pv[7] = s2.x; pv[8] = s2.y; mv[7] = ms2.x; mv[8] = ms2.y; vv[7] = vs2.x; vv[8] = vs2.y;
+        pv[9] = q4.x; pv[10] = q4.y; pv[11] = q4.z; pv[12] = q4.w;
+        mv[9] = mq4.x; mv[10] = mq4.y; mv[11] = mq4.z; mv[12] = mq4.w;
+        vv[9] = vq4.x; vv[10] = vq4.y; vv[11] = vq4.z; vv[12] = vq4.w;
+    }
+    float glob0 = 0.f, glob1 = 0.f, loc0 = 0.f, loc1 = 0.f, kfm = 0.f;
+    if (MODE == 0) {
+        glob0 = a.global_scores[2 * iz]; glob1 = a.global_scores[2 * iz + 1];
+        loc0 = a.local_scores[2 * iz]; loc1 = a.local_scores[2 * iz + 1];
+        kfm = a.kf_max[i];
+    }
+
+    // ---- backward of the activations: the expressions of sb_surfel_update_kernel / sb_dp_stage_kernel ----
+    {
+        const float y = 1.0f / (1.0f + expf(-pv[6]));
+        g[6] = g[6] * (1.0f - y) * y;
+        g[7] = g[7] * expf(pv[7]);
+        g[8] = g[8] * expf(pv[8]);
+        const float4 q = make_float4(pv[9], pv[10], pv[11], pv[12]);
+        const float4 dq = make_float4(g[9], g[10], g[11], g[12]);
+        const float len = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+        if (len > 1e-12f) {
+            const float4 r = make_float4(q.x / len, q.y / len, q.z / len, q.w / len);
+            const float rd = r.x * dq.x + r.y * dq.y + r.z * dq.z + r.w * dq.w;
+            g[9] = (dq.x - r.x * rd) / len; g[10] = (dq.y - r.y * rd) / len;
+            g[11] = (dq.z - r.z * rd) / len; g[12] = (dq.w - r.w * rd) / len;
+        } else {
+            g[9] = dq.x / 1e-12f; g[10] = dq.y / 1e-12f; g[11] = dq.z / 1e-12f; g[12] = dq.w / 1e-12f;
+        }
+    }
+    if (MODE == 1) {
+        float4* row = (float4*)(va.stage + iz * 16);
+        row[0] = make_float4(g[0], g[1], g[2], g[3]);
+        row[1] = make_float4(g[4], g[5], g[6], g[7]);
+        row[2] = make_float4(g[8], g[9], g[10], g[11]);
+        row[3] = make_float4(g[12], cur0, cur1, 0.0f);
+        return;
+    }
+
+    // ---- add_records (gaussian_model.py:163-168, gaussian_base.py:388-392) ----
+    glob0 = fminf(fmaxf(glob0 + cur0, 0.0f), 1e4f);
+    a.local_scores[2 * iz] = loc0 + cur0;
+    if (cur1 > loc1) a.local_scores[2 * iz + 1] = cur1;
+    a.global_scores[2 * iz] = glob0;
+    a.global_scores[2 * iz + 1] = fminf(fmaxf(glob1, 0.0f), 1e4f);
+    if (kfm < cur0) {
+        a.kf_max[i] = cur0;
+        a.kf_id[i] = a.kf;
+    }
+    // ---- weighting_grad (gaussian_utils.py:56-62) + masked Adam (adam.cu:9-38) ----
+    if (adam) {
+        const float gw = cur0 / (glob0 + 1e-6f + cur0);
+        float pn[13], mn[13], vn[13];
+#pragma unroll
+        for (int c = 0; c < 13; c++) {
+            pn[c] = pv[c]; mn[c] = mv[c]; vn[c] = vv[c];
+            sb_adam_scalar(pn[c], mn[c], vn[c], g[c] * gw, a.lr[SB_GRP(c)], a.b1, a.b2, a.eps);
+        }
+#pragma unroll
+        for (int c = 0; c < 7; c++) {
+            const int grp = SB_GRP(c), nc = SB_GRP_NC(grp);
+            const size_t e = iz * nc + (c - SB_GRP_C0(grp));
+            a.param[grp][e] = pn[c]; a.m[grp][e] = mn[c]; a.v[grp][e] = vn[c];
+        }
+        ((float2*)a.param[3])[i] = make_float2(pn[7], pn[8]);
+        ((float2*)a.m[3])[i] = make_float2(mn[7], mn[8]);
+        ((float2*)a.v[3])[i] = make_float2(vn[7], vn[8]);
+        ((float4*)a.param[4])[i] = make_float4(pn[9], pn[10], pn[11], pn[12]);
+        ((float4*)a.m[4])[i] = make_float4(mn[9], mn[10], mn[11], mn[12]);
+        ((float4*)a.v[4])[i] = make_float4(vn[9], vn[10], vn[11], vn[12]);
+    }
+}
+
+int sb_launch_view_update(int mode, int W, int H, float tanfovx, float tanfovy, SbViewUpdateArgs& va, cudaStream_t s) {
+    if (va.u.P == 0) return 0;
+    // Q8: the reference re-derives the image size from focal*tan in fp32 (backward.cu:1022-1023)
+    const float focal_y = H / (2.0f * tanfovy);
+    const float focal_x = W / (2.0f * tanfovx);
+    volatile float fx2 = focal_x * tanfovx;
+    volatile float fy2 = focal_y * tanfovy;
+    va.Wq = int(fx2 * 2);
+    va.Hq = int(fy2 * 2);
+    if (mode == 0) sb_view_update_kernel<0><<<(va.u.P + 255) / 256, 256, 0, s>>>(va);
+    else sb_view_update_kernel<1><<<(va.u.P + 255) / 256, 256, 0, s>>>(va);
+    sb_count_launch(1);
+    SB_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
+                                     const float* means3D, const float* scales, const float* rotations,
+                                     const float* viewmatrix, const float* projmatrix, const int* radii,
+                                     const void* geom_ws, const uint32_t* point_list, const void* image_ws,
+                                     const float* out_color, const float* out_others, const float* dL_dout_color,
+                                     const float* dL_dout_others, const uint8_t* pixel_mask, void* grad_ws, int mode,
+                                     float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+                                     const uint8_t* stable_mask, float* local_scores, float* global_scores,
+                                     float* kf_max_scores, int64_t* kf_id, int64_t kf, const float* lr, float b1,
+                                     float b2, float eps, float* stage, uint8_t* vis, void* stream) {
+    if (P < 0 || W <= 0 || H <= 0 || (mode != 0 && mode != 1)) { sb_set_error("backward_update: bad P / size / mode"); return 1; }
+    if (P == 0) return 0;
+    if (!means3D || !scales || !rotations || !viewmatrix || !projmatrix || !radii || !geom_ws || !image_ws || !grad_ws ||
+        !dL_dout_color || !dL_dout_others || !pixel_mask || !params) { sb_set_error("backward_update: NULL input"); return 1; }
+    if (mode == 0 && (!exp_avg || !exp_avg_sq || !stable_mask || !local_scores || !global_scores || !kf_max_scores ||
+                      !kf_id || !lr)) { sb_set_error("backward_update: NULL update input"); return 1; }
+    if (mode == 1 && (!stage || !vis)) { sb_set_error("backward_update: NULL stage buffers"); return 1; }
+    if ((((uintptr_t)params[3] | (uintptr_t)scales) & 7) || (((uintptr_t)params[4] | (uintptr_t)rotations | (uintptr_t)stage) & 15)) {
+        sb_set_error("backward_update: [P,2] arrays must be 8-byte, [P,4] arrays and stage rows 16-byte aligned");
+        return 1;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc;
+    if (R >= 0) {   // R < 0 (test hook): grad_ws already holds this view's accumulation records
+        SbStageScope sc(SB200_STAGE_BLEND_BWD, s);
+        SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
+        if (R > 0) {
+            rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
+                                          out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
+                                          (float*)grad_ws,
+                                          (const uint32_t*)((const char*)point_list + sb_pair_list_layout(R, W, H).masks),
+                                          nullptr, s);
+            if (rc) return rc;
+        }
+    }
+    SbViewUpdateArgs va;
+    memset(&va, 0, sizeof(va));
+    for (int g = 0; g < 5; g++) {
+        va.u.param[g] = params[g];
+        va.u.m[g] = exp_avg ? exp_avg[g] : nullptr;
+        va.u.v[g] = exp_avg_sq ? exp_avg_sq[g] : nullptr;
+        va.u.lr[g] = lr ? lr[g] : 0.f;
+    }
+    va.u.radii = radii; va.u.stable = stable_mask; va.u.local_scores = local_scores; va.u.global_scores = global_scores;
+    va.u.kf_max = kf_max_scores; va.u.kf_id = (long long*)kf_id; va.u.b1 = b1; va.u.b2 = b2; va.u.eps = eps; va.u.kf = kf;
+    va.u.P = P; va.u.mode = mode;
+    va.means3D = means3D; va.act_scales = scales; va.act_rot = rotations; va.viewmatrix = viewmatrix; va.projmatrix = projmatrix;
+    va.grad_acc = (const float*)grad_ws; va.stage = stage; va.vis = vis;
+    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    return sb_launch_view_update(mode, W, H, tanfovx, tanfovy, va, s);
 }
 
 extern "C" int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp_avg,

@@ -102,6 +102,9 @@ def _load():
     lib.sb200_surfel_update.restype = _i32
     lib.sb200_surfel_update.argtypes = ([_i32, _i32] + [_vp] * 3 + [_vp] * 5 + [_vp] * 7 + [_i64, _vp, _vp] +
                                         [_f32] * 3 + [_vp])
+    lib.sb200_backward_update.restype = _i32
+    lib.sb200_backward_update.argtypes = ([_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 15 + [_i32] + [_vp] * 8 +
+                                          [_i64, _vp] + [_f32] * 3 + [_vp] * 3)
     lib.sb200_dp_stage_bytes.restype = _sz
     lib.sb200_dp_stage_bytes.argtypes = [_i64]
     lib.sb200_dp_out_bytes.restype = _sz

@@ -204,6 +204,27 @@ class RasterWorkspace:
                                   _ptr(self.scores), _stream(self.device)), "sb200_backward")
 
 
+def backward_update(ws, mode, d_color, d_allmap, means3D, scales, rotations, bg, viewmatrix, projmatrix, tanfovx, tanfovy,
+                    params, exp_avg, exp_avg_sq, lr, stable_mask, local_scores, global_scores, kf_max_scores, kf_id, kf,
+                    stage=None, vis=None, pixel_mask=None, betas=(0.9, 0.999), eps=1e-15, reuse_records=False):
+    """sb200_backward_update (include/surfel_b200.h): the rasterizer's backward and the per-surfel update of the
+    mapping step as one call, with no dense gradient arrays in between.  mode 0 = single-GPU update, mode 1 = stage
+    rows for the multi-GPU exchange (stage / vis: raw device pointers of the rank's peer-mapped buffers)."""
+    lib = _load()
+    mask = ws.pixel_mask if pixel_mask is None else pixel_mask
+    lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
+    null = _vp(None)
+    _check(lib.sb200_backward_update(
+        ws.P, ws.W, ws.H, -1 if reuse_records else ws.R, _ptr(bg), float(tanfovx), float(tanfovy), _ptr(means3D),
+        _ptr(scales), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(ws.radii), _ptr(ws.geom),
+        _vp(ws.point_list.data_ptr()), _ptr(ws.image), _ptr(ws.color), _ptr(ws.allmap), _ptr(d_color), _ptr(d_allmap),
+        _ptr(mask), _ptr(ws.grad_ws), int(mode), _ptr_array(params),
+        _ptr_array(exp_avg) if exp_avg is not None else null, _ptr_array(exp_avg_sq) if exp_avg_sq is not None else null,
+        _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores), _ptr(kf_max_scores), _ptr(kf_id), int(kf), lr_arr,
+        float(betas[0]), float(betas[1]), float(eps), _vp(stage) if stage else null, _vp(vis) if vis else null,
+        _stream(ws.device)), "sb200_backward_update")
+
+
 def _ptr_array(tensors):
     arr = (ctypes.c_void_p * 5)()
     for i, t in enumerate(tensors):
@@ -275,8 +296,13 @@ class PeerExchange:
         """Rows per owner for P surfels (the same on every rank: multiple of 256, P <= slice * world)."""
         return ((P + self.world - 1) // self.world + 255) // 256 * 256
 
+    def stage_ptrs(self):
+        """(stage rows, visibility bytes) of this rank, for backward_update(mode=1)."""
+        return self.local + self.off_stage, self.local + self.off_vis
+
     def step(self, ws, params, exp_avg, exp_avg_sq, lr, stable_mask, local_scores, global_scores, kf_max_scores, kf_id,
-             kf_ids, betas=(0.9, 0.999), eps=1e-15):
+             kf_ids, betas=(0.9, 0.999), eps=1e-15, staged=False):
+        """staged=True: this view's stage rows were already written by backward_update(mode=1)."""
         lib = _load()
         P, dev = params[0].shape[0], self.device
         if P > self.capacity:
@@ -284,10 +310,11 @@ class PeerExchange:
         st = _stream(dev)
         S = self.slice_rows(P)
         lo, hi = min(P, self.rank * S), min(P, (self.rank + 1) * S)
-        _check(lib.sb200_dp_stage(P, _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
-                                  _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
-                                  _ptr(params[4]), _vp(self.local + self.off_stage), _vp(self.local + self.off_vis), st),
-               "sb200_dp_stage")
+        if not staged:
+            _check(lib.sb200_dp_stage(P, _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
+                                      _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
+                                      _ptr(params[4]), _vp(self.local + self.off_stage), _vp(self.local + self.off_vis), st),
+                   "sb200_dp_stage")
         self.hdl.barrier(channel=0)
         kf_arr = (ctypes.c_int64 * self.world)(*[int(k) for k in kf_ids])
         _check(lib.sb200_dp_reduce(lo, hi, self.world, self.peer_stage, self.peer_vis, kf_arr, _ptr(global_scores),

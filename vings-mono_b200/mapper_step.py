@@ -354,8 +354,9 @@ class SurfelMapper:
 
     @torch.no_grad()
     def _train_view_fused(self, view, gt, kf_id, kf_ids=None):
-        """The same iteration in 22 launches of the library: activate -> rasterizer forward -> fused loss ->
-        rasterizer backward -> one per-surfel update kernel (two around the all-reduce with world_size > 1)."""
+        """The same iteration in 21 launches of the library: activate -> rasterizer forward -> fused loss -> backward blend
+        -> one per-surfel kernel (backward preprocess + update); with world_size > 1 that kernel stages the view's rows
+        and the reduce / post kernels of the peer-memory exchange follow."""
         mp, ws = self.mod.mapping, self._ws
         prm = [getattr(self, k).data for k in GROUPS]
         st = [self.optimizer.state[getattr(self, k)] for k in GROUPS]
@@ -369,20 +370,26 @@ class SurfelMapper:
             loss, d_color, d_allmap = mp.map_loss(ws.color, ws.allmap, gt["rgb"], gt["depth"], gt["depth_cov"],
                                                   view["w2c"], self.cx, self.cy, self.fx, self.fy, self.weights,
                                                   ws=ws.loss_ws, out=ws.loss_out)
-            ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
-                        view["tanfovx"], view["tanfovy"])
-            # the only host wait of the view: the pair count, copied back right after the preprocess, with the whole
-            # view already queued.  False = the binning scratch was too small (it has been grown): run again.
+            # the only host wait of the view: the pair count, copied back right behind the preprocess; binning, forward
+            # blend and loss are already queued, so the GPU has work while the host confirms that the kept scratch was
+            # large enough.  False = it was not (it has been grown): run the forward again before anything is updated.
             if ws.confirm():
                 break
             raster = ws.forward
         book = (self._stable_mask, self._local_scores, self._global_scores, self._globalkf_max_scores, self._globalkf_id)
+        common = (d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
+                  view["tanfovx"], view["tanfovy"], prm, m, v, lr)
         if self.world_size > 1 and self.exchange == "p2p":
-            self._dpx.step(ws, prm, m, v, lr, *book, self._all_kf_ids(kf_id, kf_ids), eps=eps)
+            stage, vis = self._dpx.stage_ptrs()
+            mp.backward_update(ws, 1, *common, *book, kf_id, stage=stage, vis=vis, eps=eps)
+            self._dpx.step(ws, prm, m, v, lr, *book, self._all_kf_ids(kf_id, kf_ids), eps=eps, staged=True)
         elif self.world_size > 1:
+            ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
+                        view["tanfovx"], view["tanfovy"])
             self._nccl_step(mp, ws, prm, m, v, lr, book, self._all_kf_ids(kf_id, kf_ids), eps)
         else:
-            mp.surfel_update(mp.UPDATE_LOCAL, prm, m, v, lr, ws, *book, kf_id, eps=eps)
+            # backward blend + ONE per-surfel pass (backward preprocess, activations' backward, records, weighting, Adam)
+            mp.backward_update(ws, 0, *common, *book, kf_id, eps=eps)
         self.last_radii = ws.radii
         return loss[0]
 
