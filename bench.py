@@ -160,6 +160,10 @@ def stage_bytes(stage, c):
         "activate": 56 * P,
         "update": 49 * P + 364 * V,
         "churn": 0,
+        # multi-GPU exchange (csrc/dp_exchange.cu): per rank, stage rows of the slice's visible surfels in from every
+        # rank + result rows out; result rows of every touched surfel in + the Adam traffic of sb_surfel_update
+        "dp_reduce": 64 * V + P + (80 * min(P, 1.5 * V) + 9 * P) / max(c.get("world", 1), 1),
+        "dp_post": P + (80 + 312) * min(P, 1.5 * V),
     }[stage]
 
 
@@ -409,10 +413,19 @@ def run(emit):
         mapper.train_view = train_and_count
         mod.profile_enable(True)
         mod.profile_read()
+        dpx = getattr(mapper, "_dpx", None)
+        if dpx is not None:
+            dpx.timing = []
         timed(step_resident, args.steps, args.warmup)
         stage_ms = mod.profile_read()
         mod.profile_enable(False)
+        barrier_ms = None
+        if dpx is not None:
+            barrier_ms = {("after_stage" if ch == 0 else "after_reduce"): ms / max(n, 1) for ch, (ms, n) in dpx.read_timing().items()}
+            dpx.timing = None
         mapper.train_view = orig_train
+    else:
+        barrier_ms = None
     R_timed = R_seen
     ms_e2e, _, t2 = timed(step_e2e, args.steps, args.warmup)
     clk = clocks.summary(t0, t2) if clocks else None
@@ -451,6 +464,10 @@ def run(emit):
         out["churn"] = {"surfels_per_timed_step": P_timed, "prune_frac": CHURN_PRUNE_FRAC, "added_per_step": CHURN_ADD}
     if same_bits is not None:
         out["replicas_bit_identical"] = same_bits   # parameters, moments, score bookkeeping after the timed steps
+    if barrier_ms:
+        # device ms per view spent in the two rank barriers of the exchange (wait for the slowest rank + signalling),
+        # from the instrumented repeat (warm-up views included)
+        out["dp_barrier_ms_per_view"] = barrier_ms
     if args.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": "views/s", "cores": os.cpu_count(), "kind": "reference",
@@ -506,7 +523,7 @@ def run(emit):
     if mine:
         mod.profile_enable(False)
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
-    counters = {"P": P, "V": sum(V_seen) / len(V_seen), "HW": W * H, "tiles": tiles,
+    counters = {"P": P, "V": sum(V_seen) / len(V_seen), "HW": W * H, "tiles": tiles, "world": world,
                 "R": (sum(R_timed) / len(R_timed)) if R_timed else None,
                 "sort_passes": (higher_msb(tiles) + 7) // 8, "ref_sort_passes": (32 + higher_msb(tiles) + 7) // 8}
     out["raster"] = {"metric": "rasterizer fwd+bwd iterations/s (one view, fixed upstream gradients) through the "

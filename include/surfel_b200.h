@@ -58,7 +58,9 @@ enum {
     SB200_STAGE_UPDATE = 10,        /* fused per-surfel update (activation backward, records, weighting, Adam) */
     SB200_STAGE_CHURN = 11,         /* surfel add / prune: kNN distances, stable compaction */
     SB200_STAGE_SURFEL_SORT = 12,   /* stable onesweep sort of the visible surfels by depth (histogram + 4 passes) */
-    SB200_NUM_STAGES = 13
+    SB200_STAGE_DP_REDUCE = 13,     /* multi-GPU: reduce-scatter of the stage rows by peer loads (sb200_dp_reduce) */
+    SB200_STAGE_DP_POST = 14,       /* multi-GPU: all-gather of the result rows fused into bookkeeping + Adam (sb200_dp_post) */
+    SB200_NUM_STAGES = 15
 };
 int sb200_profile_enable(int on);
 int sb200_profile_read(double ms[SB200_NUM_STAGES], long long count[SB200_NUM_STAGES]);

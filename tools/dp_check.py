@@ -6,8 +6,8 @@ Every rank trains the same seeded map for a few optimizer steps, each step on it
 (a) the peer-memory exchange (csrc/dp_exchange.cu) and (b) the NCCL formulation, and checks:
   1. after every path the replicas are BIT-IDENTICAL on all ranks: parameters, Adam moments, and the whole score
      bookkeeping (_local_scores, _global_scores, _globalkf_max_scores, _globalkf_id);
-  2. the two exchanges agree: bit for bit at 2 ranks (a two-term sum has one order), to fp32 summation order above
-     (NCCL's ring order is not the rank order);
+  2. the two exchanges agree to gradient jitter (they are two runs: every backward blend sums with atomics in its
+     own order), moments to 2e-3 relative L1, parameters and scores to 1e-3;
   3. rank 0: the step count, surfels updated, and that a prune + densify in between keeps the ranks in lockstep.
 Prints one JSON line on rank 0; exit code 1 on any mismatch."""
 import json
@@ -95,21 +95,24 @@ def main():
         report[exchange + "_P_final"] = m.P
         ok &= same
         del m
-    # 2. the two exchanges agree
+    # 2. the two exchanges agree -- to tolerance: they are two RUNS (each backward blend sums with atomics in its own
+    # order, and the p2p path inlines the backward-preprocess arithmetic into another kernel), so bits cannot match
     worst = 0.0
     for k in states["p2p"]:
         a, b = states["p2p"][k], states["nccl"][k]
-        if world == 2 or not a.dtype.is_floating_point:
-            eq = torch.equal(a, b) if k != "_globalkf_id" or world == 2 else float((a != b).float().mean()) < 1e-3
-            if not eq:
-                ok = False
-                report.setdefault("mismatch", []).append(k)
+        if k == "_globalkf_id":
+            bad = float((a != b).float().mean()) >= 1e-3      # arg-max ties decided by ulp-level score noise
+        elif k == "_stable_mask":
+            bad = not torch.equal(a, b)
         else:
             rel = float((a.double() - b.double()).abs().sum() / b.double().abs().sum().clamp(min=1e-30))
             worst = max(worst, rel)
-            if rel > 2e-3:   # Adam turns summation-order noise into sign-like flips on a few elements (see tests/util.py)
-                ok = False
-                report.setdefault("mismatch", []).append((k, rel))
+            # moments are linear / quadratic in the gradients (2e-3, as tests/util.py); parameters move by lr-sized
+            # steps, so their relative L1 difference is far smaller
+            bad = rel > (2e-3 if k[0] in "mv" and k[1] == "_" else 1e-3)
+        if bad:
+            ok = False
+            report.setdefault("mismatch", []).append(k)
     report["p2p_vs_nccl_worst_rel"] = worst
     moved = float((states["p2p"]["_xyz"][:1000] != scene["means3D"][:1000].to(dev)).float().mean())
     report["moved_frac_first_1000"] = moved

@@ -29,6 +29,7 @@ STAGE_OF = [
     ("sb_onesweep_kernel<16>", "sort"), ("sb_pair_offsets", "duplicate"), ("sb_duplicate", "duplicate"),
     ("sb_tile_scan", "ranges"), ("sb_blend_forward", "blend_fwd"), ("sb_blend_backward", "blend_bwd"),
     ("sb_loss", "map_loss"), ("sb_ssim", "map_loss"), ("sb_geom_loss", "map_loss"), ("sb_surfel_update", "update"),
+    ("sb_view_update", "update"), ("sb_dp_", "update"),
     ("sb_adam", "adam"),
 ]
 UNIT = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "inst": 1.0}

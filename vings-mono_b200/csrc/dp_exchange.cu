@@ -266,7 +266,7 @@ int sb200_dp_reduce(int lo, int hi, int n_ranks, const void* const* peer_stage, 
     }
     a.global_scores = global_scores; a.out = out; a.upd = upd; a.lo = lo; a.hi = hi; a.n_ranks = n_ranks;
     cudaStream_t s = (cudaStream_t)stream;
-    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    SbStageScope sc(SB200_STAGE_DP_REDUCE, s);
     sb_dp_reduce_kernel<<<(hi - lo + 255) / 256, 256, 0, s>>>(a);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
@@ -299,7 +299,7 @@ int sb200_dp_post(int P, int slice, int n_ranks, const void* const* peer_out, co
     a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;
     a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.slice = slice;
     cudaStream_t s = (cudaStream_t)stream;
-    SbStageScope sc(SB200_STAGE_UPDATE, s);
+    SbStageScope sc(SB200_STAGE_DP_POST, s);
     sb_dp_post_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());

@@ -238,7 +238,7 @@ def release_workspaces():
 
 
 STAGES = ("preprocess", "duplicate", "sort", "ranges", "blend_fwd", "blend_bwd", "preprocess_bwd", "adam",
-          "map_loss", "activate", "update", "churn", "surfel_sort")
+          "map_loss", "activate", "update", "churn", "surfel_sort", "dp_reduce", "dp_post")
 
 
 def profile_enable(on=True):

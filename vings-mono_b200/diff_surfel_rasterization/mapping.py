@@ -289,8 +289,31 @@ class PeerExchange:
         self.peer_stage, self.peer_vis = arr(self.off_stage), arr(self.off_vis)
         self.peer_out, self.peer_upd = arr(self.off_out), arr(self.off_upd)
         self.local = bases[self.rank]
+        self.timing = None   # set to [] to collect CUDA-event pairs around the two barriers (bench.py, tools/)
         torch.cuda.synchronize(device)
         self.hdl.barrier(channel=0)   # every rank has zeroed its buffer before anyone reads it
+
+    def _barrier(self, channel):
+        """Barrier over the ranks on the current stream (signal pads of the symmetric allocation).  Its device time is
+        the wait for the slowest rank of the step plus the signalling itself."""
+        if self.timing is None:
+            self.hdl.barrier(channel=channel)
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        self.hdl.barrier(channel=channel)
+        e1.record()
+        self.timing.append((channel, e0, e1))
+
+    def read_timing(self):
+        """{barrier channel: (total ms, count)} since timing was switched on; waits for the events."""
+        out = {}
+        for ch, e0, e1 in self.timing or []:
+            e1.synchronize()
+            ms, n = out.get(ch, (0.0, 0))
+            out[ch] = (ms + e0.elapsed_time(e1), n + 1)
+        self.timing = []
+        return out
 
     def slice_rows(self, P):
         """Rows per owner for P surfels (the same on every rank: multiple of 256, P <= slice * world)."""
@@ -315,11 +338,11 @@ class PeerExchange:
                                       _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
                                       _ptr(params[4]), _vp(self.local + self.off_stage), _vp(self.local + self.off_vis), st),
                    "sb200_dp_stage")
-        self.hdl.barrier(channel=0)
+        self._barrier(0)
         kf_arr = (ctypes.c_int64 * self.world)(*[int(k) for k in kf_ids])
         _check(lib.sb200_dp_reduce(lo, hi, self.world, self.peer_stage, self.peer_vis, kf_arr, _ptr(global_scores),
                                    _vp(self.local + self.off_out), _vp(self.local + self.off_upd), st), "sb200_dp_reduce")
-        self.hdl.barrier(channel=1)
+        self._barrier(1)
         lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
         _check(lib.sb200_dp_post(P, S, self.world, self.peer_out, self.peer_upd, _ptr_array(params), _ptr_array(exp_avg),
                                  _ptr_array(exp_avg_sq), _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores),
