@@ -398,6 +398,8 @@ def run(emit):
     # warm-up launches are in the counter too; scale launches to the timed steps only
     launches = launches * args.steps // (args.steps + args.warmup)
     same_bits = replicas_identical(mapper)
+    if getattr(mapper, "_dpx", None) is not None:
+        mapper._dpx.check()   # no kernel of the exchange ever gave up waiting for a peer
     P_timed = P_seen[args.warmup:] if churn else [P]
     # per-stage device times (roofline): the same K steps once more with the library's stage events switched on
     # (two event records per stage cost ~1.5 % of a view, so they stay out of the pass `value` is taken from)
@@ -413,19 +415,10 @@ def run(emit):
         mapper.train_view = train_and_count
         mod.profile_enable(True)
         mod.profile_read()
-        dpx = getattr(mapper, "_dpx", None)
-        if dpx is not None:
-            dpx.timing = []
         timed(step_resident, args.steps, args.warmup)
         stage_ms = mod.profile_read()
         mod.profile_enable(False)
-        barrier_ms = None
-        if dpx is not None:
-            barrier_ms = {("after_stage" if ch == 0 else "after_reduce"): ms / max(n, 1) for ch, (ms, n) in dpx.read_timing().items()}
-            dpx.timing = None
         mapper.train_view = orig_train
-    else:
-        barrier_ms = None
     R_timed = R_seen
     ms_e2e, _, t2 = timed(step_e2e, args.steps, args.warmup)
     clk = clocks.summary(t0, t2) if clocks else None
@@ -464,10 +457,6 @@ def run(emit):
         out["churn"] = {"surfels_per_timed_step": P_timed, "prune_frac": CHURN_PRUNE_FRAC, "added_per_step": CHURN_ADD}
     if same_bits is not None:
         out["replicas_bit_identical"] = same_bits   # parameters, moments, score bookkeeping after the timed steps
-    if barrier_ms:
-        # device ms per view spent in the two rank barriers of the exchange (wait for the slowest rank + signalling),
-        # from the instrumented repeat (warm-up views included)
-        out["dp_barrier_ms_per_view"] = barrier_ms
     if args.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": "views/s", "cores": os.cpu_count(), "kind": "reference",

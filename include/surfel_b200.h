@@ -211,8 +211,8 @@ int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp
  *   means3D / scales / rotations: the rasterizer inputs of this view (activated); params: the five RAW parameter arrays
  *   (params[0] is means3D); the rest as sb200_surfel_update.
  *   mode 0: single-GPU update (SB200_UPDATE_LOCAL semantics).
- *   mode 1: multi-GPU stage - writes what sb200_dp_stage writes (stage rows of visible surfels, vis bytes) and updates
- *           nothing; exp_avg .. lr may be NULL.
+ *   mode 1: multi-GPU stage - does what sb200_dp_stage does (stage rows of visible surfels, visibility bytes, signal to
+ *           the peers) on the exchange handle `dp` and updates nothing; exp_avg .. lr may be NULL.
  *   R < 0 (test hook): skip the blend, grad_ws already holds the view's accumulation records. */
 int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
                           const float* means3D, const float* scales, const float* rotations,
@@ -223,37 +223,43 @@ int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float
                           float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
                           const uint8_t* stable_mask, float* local_scores, float* global_scores,
                           float* kf_max_scores, int64_t* kf_id, int64_t kf, const float* lr, float b1,
-                          float b2, float eps, float* stage, uint8_t* vis, void* stream);
+                          float b2, float eps, void* dp, void* stream);
 
 /* ---- multi-GPU exchange of the mapping step over NVLink peer memory ----------------------
  * One optimizer step takes ONE view per rank (window views partitioned over the GPUs of a box, surfels replicated).
- * The three calls below replace "sb200_surfel_update(DP_PRE) -> NCCL all-reduce of [16,P] -> sb200_surfel_update(
- * DP_POST)" by kernels that read their peers' buffers directly; the caller provides peer-mapped allocations (one
- * pointer per rank to the same buffer of that rank, e.g. torch symmetric memory) and a barrier over the ranks between
- * the calls (all three are stream ordered).  Surfel i is owned by rank i / slice.
- *   sb200_dp_stage : backward of the activations; for a visible surfel (radii > 0) writes its 13 raw-parameter
- *                    gradients and two scores to stage[i] (16 floats), vis[i] = radii > 0.  Local buffers of the rank
- *                    (sb200_dp_stage_bytes(P) bytes, P bytes).
- *   sb200_dp_reduce: for the owned surfels lo <= i < hi: loads the stage rows of every rank q with peer_vis[q][i],
- *                    applies weighting_grad per view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views in
- *                    rank order: gradient sum, score-0 sum, score-1 max, first arg-max of score 0 with its keyframe id
- *                    kf_ids[q] (HOST array, one id per rank) -> out[i - lo] (20 floats), upd[i - lo] = seen by any view.
- *   sb200_dp_post  : every rank, every surfel: loads the owner's result row (peer_out / peer_upd), applies add_records
- *                    (scripts/gaussian/gaussian_model.py:163-168) for the folded views and the masked Adam step
- *                    (cuda_rasterizer/adam.cu:9-38) to the local replica.  All ranks read the same bytes: the replicas
- *                    stay bit-identical, and equal a single process that takes the same views in rank order.
- * params / exp_avg / exp_avg_sq / lr: as sb200_surfel_update.  peer_*: HOST arrays of n_ranks (<= 16) device pointers. */
-size_t sb200_dp_stage_bytes(int64_t P);
-size_t sb200_dp_out_bytes(int64_t slice);
-int sb200_dp_stage(int P, const float* d_means3D, const float* d_colors, const float* d_opacity, const float* d_scales,
-                   const float* d_rotations, const float* cur_scores, const int* radii, const float* opacity_raw,
-                   const float* scaling_raw, const float* rotation_raw, float* stage, uint8_t* vis, void* stream);
-int sb200_dp_reduce(int lo, int hi, int n_ranks, const void* const* peer_stage, const void* const* peer_vis,
-                    const int64_t* kf_ids, const float* global_scores, float* out, uint8_t* upd, void* stream);
-int sb200_dp_post(int P, int slice, int n_ranks, const void* const* peer_out, const void* const* peer_upd,
-                  float* const* params, float* const* exp_avg, float* const* exp_avg_sq, const uint8_t* stable_mask,
-                  float* local_scores, float* global_scores, float* kf_max_scores, int64_t* kf_id, const float* lr,
-                  float b1, float b2, float eps, void* stream);
+ * The calls below replace "sb200_surfel_update(DP_PRE) -> NCCL all-reduce of [16,P] -> sb200_surfel_update(DP_POST)" by
+ * three kernels that read their peers' buffers directly and hand over to each other through flags in those buffers
+ * (system-scope release / acquire; no barrier kernel, no collective call).  Surfel i is owned by rank i / slice.
+ *   sb200_dp_create : rank's handle.  peer_bases: HOST array of n_ranks (<= 16) DEVICE pointers, entry q = rank q's
+ *                     exchange buffer of sb200_dp_buffer_bytes(capacity, n_ranks) bytes, zero-filled, mapped into this
+ *                     process (e.g. one torch symmetric-memory allocation per rank); every rank calls the three step
+ *                     functions in lockstep, once per optimizer step, each on its own stream.
+ *   sb200_dp_stage  : backward of the activations; for a visible surfel (radii > 0) writes its 13 raw-parameter
+ *                     gradients and two scores to the rank's stage row (16 floats) and its visibility byte; the last
+ *                     CTA signals the peers.  (sb200_backward_update with mode 1 does the same straight from the
+ *                     accumulation records.)
+ *   sb200_dp_reduce : waits for every peer's stage; for the owned surfels loads the stage rows of every rank that saw
+ *                     them, applies weighting_grad per view (scripts/gaussian/gaussian_utils.py:56-62) and folds the
+ *                     views in rank order: gradient sum, score-0 sum, score-1 max, first arg-max of score 0 with its
+ *                     keyframe id kf_ids[q] (HOST array, one id per rank) -> the owner's result row (20 floats); signals.
+ *   sb200_dp_post   : waits for every peer's reduce; every rank, every surfel some view saw: loads the owner's result
+ *                     row, applies add_records (scripts/gaussian/gaussian_model.py:163-168) for the folded views and the
+ *                     masked Adam step (cuda_rasterizer/adam.cu:9-38) to the local replica.  All ranks read the same
+ *                     bytes: the replicas stay bit-identical, and equal a single process taking the views in rank order.
+ *   sb200_dp_error  : non-zero if a wait ever gave up (a peer did not signal within 20 s); synchronises the stream.
+ * params / exp_avg / exp_avg_sq / lr: as sb200_surfel_update. */
+size_t sb200_dp_buffer_bytes(int64_t capacity, int n_ranks);
+void* sb200_dp_create(int rank, int n_ranks, int64_t capacity, const void* const* peer_bases);
+void sb200_dp_destroy(void* handle);
+int sb200_dp_slice(void* handle, int P);
+int sb200_dp_error(void* handle, void* stream);
+int sb200_dp_stage(void* handle, int P, const float* d_means3D, const float* d_colors, const float* d_opacity,
+                   const float* d_scales, const float* d_rotations, const float* cur_scores, const int* radii,
+                   const float* opacity_raw, const float* scaling_raw, const float* rotation_raw, void* stream);
+int sb200_dp_reduce(void* handle, int P, const int64_t* kf_ids, const float* global_scores, void* stream);
+int sb200_dp_post(void* handle, int P, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+                  const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
+                  int64_t* kf_id, const float* lr, float b1, float b2, float eps, void* stream);
 
 /* ---- surfel add / prune churn --------------------------------------------
  * sb200_knn_mean_dist2: out[i] = mean of the squared distances from points[i] to its 3 nearest OTHER points, i.e.

@@ -314,32 +314,37 @@ def test_peer_exchange_kernels_equal_the_batched_step_on_one_device():
         return ([p.clone() for p in prm], [x["exp_avg"].clone() for x in st], [x["exp_avg_sq"].clone() for x in st],
                 [m._local_scores.clone(), m._global_scores.clone(), m._globalkf_max_scores.clone(), m._globalkf_id.clone()])
 
-    # ---- (A) the peer-memory kernels, ranks emulated ----
+    # ---- (A) the peer-memory kernels, ranks emulated: N exchange buffers on this device, one handle per "rank".  The
+    # kernels' flag hand-offs run for real (all stage kernels are queued before any reduce, all reduces before any
+    # post, so every wait finds its flags already set) ----
     pa, ma, va, ba = state()
     vp = ctypes.c_void_p
     st_ = vp(torch.cuda.current_stream().cuda_stream)
-    S = ((P + N - 1) // N + 255) // 256 * 256
-    stage = [torch.full((lib.sb200_dp_stage_bytes(P) // 4,), float("nan"), device=dev) for _ in range(N)]
-    vis = [torch.full((P,), 7, dtype=torch.uint8, device=dev) for _ in range(N)]
-    out = [torch.full((lib.sb200_dp_out_bytes(S) // 4,), float("nan"), device=dev) for _ in range(N)]
-    upd = [torch.full((S,), 7, dtype=torch.uint8, device=dev) for _ in range(N)]
-    parr = lambda ts: (vp * N)(*[t.data_ptr() for t in ts])
+    nbytes = lib.sb200_dp_buffer_bytes(P, N)
+    bufs = [torch.zeros(nbytes, dtype=torch.uint8, device=dev) for _ in range(N)]
+    bases = (vp * N)(*[t.data_ptr() for t in bufs])
+    handles = [lib.sb200_dp_create(r, N, P, bases) for r in range(N)]
+    assert all(handles), lib.sb200_last_error()
+    S = lib.sb200_dp_slice(vp(handles[0]), P)
+    assert S % 256 == 0 and S * N >= P
     for q in range(N):
         ws = wss[q]
-        assert lib.sb200_dp_stage(P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()), vp(ws.d_opacity.data_ptr()),
-                                  vp(ws.d_scales.data_ptr()), vp(ws.d_rot.data_ptr()), vp(ws.scores.data_ptr()),
-                                  vp(ws.radii.data_ptr()), vp(prm[2].data_ptr()), vp(prm[3].data_ptr()),
-                                  vp(prm[4].data_ptr()), vp(stage[q].data_ptr()), vp(vis[q].data_ptr()), st_) == 0
+        assert lib.sb200_dp_stage(vp(handles[q]), P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()),
+                                  vp(ws.d_opacity.data_ptr()), vp(ws.d_scales.data_ptr()), vp(ws.d_rot.data_ptr()),
+                                  vp(ws.scores.data_ptr()), vp(ws.radii.data_ptr()), vp(prm[2].data_ptr()),
+                                  vp(prm[3].data_ptr()), vp(prm[4].data_ptr()), st_) == 0, lib.sb200_last_error()
     kf_arr = (ctypes.c_int64 * N)(*kf_ids)
     for r in range(N):
-        lo, hi = min(P, r * S), min(P, (r + 1) * S)
-        assert lib.sb200_dp_reduce(lo, hi, N, parr(stage), parr(vis), kf_arr, vp(ba[1].data_ptr()),
-                                   vp(out[r].data_ptr()), vp(upd[r].data_ptr()), st_) == 0, lib.sb200_last_error()
+        assert lib.sb200_dp_reduce(vp(handles[r]), P, kf_arr, vp(ba[1].data_ptr()), st_) == 0, lib.sb200_last_error()
     arr5 = lambda ts: (vp * 5)(*[t.data_ptr() for t in ts])
-    assert lib.sb200_dp_post(P, S, N, parr(out), parr(upd), arr5(pa), arr5(ma), arr5(va), vp(stable.data_ptr()),
+    # rank 0's replica is updated; the other "ranks" would do the same from the same result rows
+    assert lib.sb200_dp_post(vp(handles[0]), P, arr5(pa), arr5(ma), arr5(va), vp(stable.data_ptr()),
                              vp(ba[0].data_ptr()), vp(ba[1].data_ptr()), vp(ba[2].data_ptr()), vp(ba[3].data_ptr()),
                              (ctypes.c_float * 5)(*lr), 0.9, 0.999, 1e-15, st_) == 0, lib.sb200_last_error()
     torch.cuda.synchronize()
+    for r in range(N):
+        assert lib.sb200_dp_error(vp(handles[r]), st_) == 0, lib.sb200_last_error()
+        lib.sb200_dp_destroy(vp(handles[r]))
 
     # ---- (B) the NCCL formulation with the collectives replaced by torch reductions over the same rows ----
     pb, mb, vb, bb = state()
@@ -430,23 +435,30 @@ def test_backward_update_equals_backward_then_update():
         assert not torch.equal(x, p0) and torch.equal(y[stable], p0[stable])
         vis = ws.radii > 0
         assert torch.equal(y[~vis], p0[~vis])
-    # mode 1: the multi-GPU stage rows, against sb200_dp_stage on the dense outputs
+    # mode 1: the multi-GPU stage rows, against sb200_dp_stage on the dense outputs (one-rank exchange handles)
     vp = ctypes.c_void_p
     st_ = vp(torch.cuda.current_stream().cuda_stream)
-    stage_a = torch.zeros(lib.sb200_dp_stage_bytes(P) // 4, device=dev)
-    stage_b = torch.zeros_like(stage_a)
-    vis_a, vis_b = torch.full((P,), 7, dtype=torch.uint8, device=dev), torch.full((P,), 7, dtype=torch.uint8, device=dev)
-    assert lib.sb200_dp_stage(P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()), vp(ws.d_opacity.data_ptr()),
+    nbytes = lib.sb200_dp_buffer_bytes(P, 1)
+    buf_a, buf_b = torch.zeros(nbytes, dtype=torch.uint8, device=dev), torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    buf_a[64 * P:65 * P] = 7
+    buf_b[64 * P:65 * P] = 7      # visibility bytes start out as junk
+    ha = lib.sb200_dp_create(0, 1, P, (vp * 1)(buf_a.data_ptr()))
+    hb = lib.sb200_dp_create(0, 1, P, (vp * 1)(buf_b.data_ptr()))
+    assert lib.sb200_dp_stage(vp(ha), P, vp(ws.d_means3D.data_ptr()), vp(ws.d_colors.data_ptr()), vp(ws.d_opacity.data_ptr()),
                               vp(ws.d_scales.data_ptr()), vp(ws.d_rot.data_ptr()), vp(ws.scores.data_ptr()),
                               vp(ws.radii.data_ptr()), vp(prm[2].data_ptr()), vp(prm[3].data_ptr()),
-                              vp(prm[4].data_ptr()), vp(stage_a.data_ptr()), vp(vis_a.data_ptr()), st_) == 0
+                              vp(prm[4].data_ptr()), st_) == 0
     before = state()
     mp.backward_update(ws, 1, d_color, d_allmap, prm[0], scales, rot, m.bg, vd["viewmatrix"], vd["projmatrix"],
                        vd["tanfovx"], vd["tanfovy"], prm, None, None, lr, None, None, None, None, None, 7,
-                       stage=stage_b.data_ptr(), vis=vis_b.data_ptr(), reuse_records=True)
+                       dp=hb, reuse_records=True)
     torch.cuda.synchronize()
+    stage_a, stage_b = buf_a[:64 * P].view(torch.float32), buf_b[:64 * P].view(torch.float32)
+    vis_a, vis_b = buf_a[64 * P:65 * P], buf_b[64 * P:65 * P]   # layout: stage rows f32[P][16], then the vis bytes
     assert torch.equal(vis_a, vis_b) and torch.equal(vis_a.bool(), ws.radii > 0)
-    assert util.rel_err(stage_b, stage_a) < 1e-6
-    assert torch.equal(stage_b.view(P, 16)[:, 13:15][vis_a.bool()], ws.scores[vis_a.bool()])
+    seen = vis_a.bool()
+    assert util.rel_err(stage_b.view(P, 16)[seen], stage_a.view(P, 16)[seen]) < 1e-6
+    assert torch.equal(stage_b.view(P, 16)[:, 13:15][seen], ws.scores[seen])
+    lib.sb200_dp_destroy(vp(ha)); lib.sb200_dp_destroy(vp(hb))
     for x, y in zip(before[0] + before[1] + before[2] + before[3], state()[0] + state()[1] + state()[2] + state()[3]):
         assert torch.equal(x, y)   # mode 1 updates nothing

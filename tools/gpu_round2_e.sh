@@ -7,7 +7,7 @@ N=${1:-2}
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 nvidia-smi topo -m > $O/r02e_topo_${N}gpu.txt 2>&1
 timeout 300 $RUN --master-port 29511 tools/dp_check.py > $O/r02e_dp_check_${N}gpu.json 2> $O/r02e_dp_check_${N}gpu.err; echo "dp_check rc=$?"; cat $O/r02e_dp_check_${N}gpu.json; tail -5 $O/r02e_dp_check_${N}gpu.err
-python -m pytest tests/test_multigpu.py -m gpu -q > $O/r02e_pytest_multigpu.log 2>&1; tail -3 $O/r02e_pytest_multigpu.log
+python -m pytest tests/test_mapping.py tests/test_multigpu.py -m gpu -q -x > $O/r02e_pytest_multigpu.log 2>&1; tail -3 $O/r02e_pytest_multigpu.log
 timeout 600 $RUN --master-port 29512 bench.py --gpus $N --steps 5 --warmup 3 > $O/r02e_bench_b200_C2_${N}gpu.json 2> $O/r02e_bench_b200_C2_${N}gpu.err; echo "bench p2p rc=$?"; tail -3 $O/r02e_bench_b200_C2_${N}gpu.err
 SB200_DP_EXCHANGE=nccl timeout 600 $RUN --master-port 29513 bench.py --gpus $N --steps 5 --warmup 3 --no-extras > $O/r02e_bench_b200_C2_${N}gpu_nccl.json 2> $O/r02e_bench_b200_C2_${N}gpu_nccl.err; echo "bench nccl rc=$?"; tail -3 $O/r02e_bench_b200_C2_${N}gpu_nccl.err
 python - <<'PY'

@@ -13,39 +13,38 @@
 //   sb_dp_stage_kernel   (every rank, all surfels)   backward of the three activations; a visible surfel's 13
 //                        raw-parameter gradients + its two scores go into the rank's OWN stage row (64 B), its
 //                        visibility into a byte array.  Local stores only.
-//   -- barrier over the ranks (signal pads of the symmetric allocation; Python side) --
+//   -- hand-off: the LAST CTA of the stage kernel release-stores the step number into every peer's flag block; every
+//      CTA of the next kernel spins (acquire, system scope) on its own rank's flags before it touches peer rows --
 //   sb_dp_reduce_kernel  (rank r, its slice of the surfels)   a reduce-scatter by peer LOADS: for the surfels it
 //                        owns the rank reads the stage rows of the ranks that saw them, applies weighting_grad per
 //                        view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views IN RANK ORDER into one
 //                        80-B result row: gradient sum, add_records' running quantities (gaussian_model.py:163-168:
 //                        score sum, max of the second score, first arg-max of the first score and its keyframe id).
-//   -- barrier --
+//   -- same hand-off on a second flag channel --
 //   sb_dp_post_kernel    (every rank, all surfels)   an all-gather fused with its consumer: reads the result row of
 //                        every touched surfel from its owner (peer load for 7/8 of them) and applies the score
 //                        bookkeeping and the masked Adam step to the local replica.  Every rank consumes the same
 //                        80 bytes, so the replicas stay bit-identical by construction.
 //
+// There is no barrier kernel and no collective call: the only cross-GPU synchronisation is those two flag hand-offs
+// (monotonic step counters, never reset), and they also order the buffers' reuse -- a rank's next stage kernel
+// follows its own post kernel, which has waited for every peer's reduce (the readers of its stage rows); its next
+// reduce waits for every peer's next stage, which follows that peer's post (the readers of its result rows).
+//
 // Bytes over NVLink per rank and step at C2 on 8 GPUs: stage rows 7/8 * (P/8) * 8 * 0.41 * 64 B = 22 MB in, result
 // rows 7/8 * ~0.6 P * 80 B = 50 MB in, against 2 * 7/8 * 77 MB = 134 MB for the dense all-reduce.
-#include "common.cuh"
+#include "dp_sync.cuh"
+#include <string.h>
 #include "../../include/surfel_b200.h"
 
-#define SB_DP_MAX_RANKS 16
 #define SB_DP_STAGE_F 16   // floats per stage row: 13 gradients, score 0, score 1, pad
 #define SB_DP_OUT_F 20     // floats per result row: 13 gradients, score sum, score-1 max, score-0 max, kf id (2 words), pad 2
 
-// Loads of memory another GPU wrote in an earlier kernel (ordered by the ranks' barrier): system-scope relaxed loads,
-// never served from this SM's L1.
-__device__ __forceinline__ float4 sb_ld_sys_f4(const float4* p) {
-    float4 v;
-    asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-    return v;
-}
-__device__ __forceinline__ uint32_t sb_ld_sys_u8(const uint8_t* p) {
-    uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
+// Loads of rows another GPU wrote: the writer's kernel released them with a system-scope store of the step number,
+// this kernel acquired that flag (sb_dp_wait) before any thread gets here, so ordinary loads observe them; .cg keeps
+// them out of L1 (they are read once).
+__device__ __forceinline__ float4 sb_ld_peer_f4(const float4* p) { return __ldcg(p); }
+__device__ __forceinline__ uint32_t sb_ld_peer_u8(const uint8_t* p) { return (uint32_t)__ldcg(p); }
 
 struct SbDpStageArgs {
     const float* d_means3D; const float* d_colors; const float* d_opacity; const float* d_scales; const float* d_rot;
@@ -53,9 +52,10 @@ struct SbDpStageArgs {
     const float* opacity_raw; const float* scaling_raw; const float* rotation_raw;
     float* stage; uint8_t* vis;
     int P;
+    SbDpSync sync;
 };
 
-__global__ void __launch_bounds__(256) sb_dp_stage_kernel(SbDpStageArgs a) {
+__device__ __forceinline__ void sb_dp_stage_body(const SbDpStageArgs& a) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.P) return;
     const bool visible = a.radii[i] > 0;
@@ -104,9 +104,10 @@ struct SbDpReduceArgs {
     float* out;                   // [slice, SB_DP_OUT_F] this rank's result rows
     uint8_t* upd;                 // [slice] 1 = some view saw the surfel
     int lo, hi, n_ranks;
+    SbDpSync sync;
 };
 
-__global__ void __launch_bounds__(256) sb_dp_reduce_kernel(SbDpReduceArgs a) {
+__device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
     const int i = a.lo + blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.hi) return;
     const size_t iz = (size_t)i;
@@ -118,9 +119,9 @@ __global__ void __launch_bounds__(256) sb_dp_reduce_kernel(SbDpReduceArgs a) {
     long long kf_arg = 0;
     bool any = false;
     for (int q = 0; q < a.n_ranks; q++) {   // rank order = the order a single process would take the views in
-        if (!sb_ld_sys_u8(a.peer_vis[q] + iz)) continue;
+        if (!sb_ld_peer_u8(a.peer_vis[q] + iz)) continue;
         const float4* row = (const float4*)(a.peer_stage[q] + iz * SB_DP_STAGE_F);
-        const float4 r0 = sb_ld_sys_f4(row), r1 = sb_ld_sys_f4(row + 1), r2 = sb_ld_sys_f4(row + 2), r3 = sb_ld_sys_f4(row + 3);
+        const float4 r0 = sb_ld_peer_f4(row), r1 = sb_ld_peer_f4(row + 1), r2 = sb_ld_peer_f4(row + 2), r3 = sb_ld_peer_f4(row + 3);
         const float c0 = r3.y, c1 = r3.z;
         // weighting_grad with this view's score counted into the global score (add_records runs first), as in the
         // single-GPU pass; the global score itself is updated once, from the sum, by sb_dp_post_kernel
@@ -153,21 +154,22 @@ struct SbDpPostArgs {
     float lr[5];
     float b1, b2, eps;
     int P, slice;
+    SbDpSync sync;
 };
 
 #define SB_GRP(c) ((c) < 3 ? 0 : (c) < 6 ? 1 : (c) < 7 ? 2 : (c) < 9 ? 3 : 4)
 #define SB_GRP_NC(g) ((g) == 0 ? 3 : (g) == 1 ? 3 : (g) == 2 ? 1 : (g) == 3 ? 2 : 4)
 #define SB_GRP_C0(g) ((g) == 0 ? 0 : (g) == 1 ? 3 : (g) == 2 ? 6 : (g) == 3 ? 7 : 9)
 
-__global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
+__device__ __forceinline__ void sb_dp_post_body(const SbDpPostArgs& a) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.P) return;
     const size_t iz = (size_t)i;
     const int owner = i / a.slice, li = i - owner * a.slice;
-    if (!sb_ld_sys_u8(a.peer_upd[owner] + li)) return;   // no view saw it: add_records with zero scores is the identity
+    if (!sb_ld_peer_u8(a.peer_upd[owner] + li)) return;   // no view saw it: add_records with zero scores is the identity
     const float4* o = (const float4*)(a.peer_out[owner] + (size_t)li * SB_DP_OUT_F);
-    const float4 r0 = sb_ld_sys_f4(o), r1 = sb_ld_sys_f4(o + 1), r2 = sb_ld_sys_f4(o + 2), r3 = sb_ld_sys_f4(o + 3),
-                 r4 = sb_ld_sys_f4(o + 4);
+    const float4 r0 = sb_ld_peer_f4(o), r1 = sb_ld_peer_f4(o + 1), r2 = sb_ld_peer_f4(o + 2), r3 = sb_ld_peer_f4(o + 3),
+                 r4 = sb_ld_peer_f4(o + 4);
     const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
     const float s0_sum = r3.y, s1_max = r3.z, s0_max = r3.w;
     const long long kf_arg = ((long long)__float_as_int(r4.y) << 32) | (unsigned int)__float_as_int(r4.x);
@@ -225,82 +227,188 @@ __global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
     }
 }
 
+__global__ void __launch_bounds__(256) sb_dp_stage_kernel(SbDpStageArgs a) {
+    sb_dp_stage_body(a);
+    sb_dp_signal(a.sync, 0);
+}
+__global__ void __launch_bounds__(256) sb_dp_reduce_kernel(SbDpReduceArgs a) {
+    sb_dp_wait(a.sync, 0);
+    sb_dp_reduce_body(a);
+    sb_dp_signal(a.sync, 1);
+}
+__global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
+    sb_dp_wait(a.sync, 1);
+    sb_dp_post_body(a);
+}
+
+// ---- host side: one exchange handle per rank (layout of the peer-mapped buffer, peer pointers, step counter) ----
+struct SbDpLayout { size_t stage, vis, out, upd, flags, counter, error, total; int64_t slice_cap; };
+static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
+    SbDpLayout L;
+    const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
+    L.slice_cap = (int64_t)((((cap + n_ranks - 1) / n_ranks) + 255) / 256 * 256);
+    size_t o = 0;
+    L.stage = o;   o = sb_align(o + cap * SB_DP_STAGE_F * 4);
+    L.vis = o;     o = sb_align(o + cap);
+    L.out = o;     o = sb_align(o + (size_t)L.slice_cap * SB_DP_OUT_F * 4);
+    L.upd = o;     o = sb_align(o + (size_t)L.slice_cap);
+    L.flags = o;   o = sb_align(o + 2 * SB_DP_MAX_RANKS * 4);
+    L.counter = o; o = sb_align(o + 2 * 4);
+    L.error = o;   o = sb_align(o + 4);
+    L.total = o;
+    return L;
+}
+
+struct SbDpHandle {
+    int rank, n_ranks;
+    int64_t capacity;
+    SbDpLayout L;
+    char* base[SB_DP_MAX_RANKS];
+    uint32_t step;
+};
+
+static SbDpSync sb_dp_sync_of(const SbDpHandle* h) {
+    SbDpSync y;
+    memset(&y, 0, sizeof(y));
+    for (int q = 0; q < h->n_ranks; q++) y.peer_flags[q] = (uint32_t*)(h->base[q] + h->L.flags);
+    y.counter = (uint32_t*)(h->base[h->rank] + h->L.counter);
+    y.error = (uint32_t*)(h->base[h->rank] + h->L.error);
+    y.step = h->step;
+    y.rank = h->rank;
+    y.n_ranks = h->n_ranks;
+    return y;
+}
+
+// used by sb200_backward_update(mode 1) in surfel_update.cu
+int sb_dp_begin_step(void* handle, int P, float** stage, uint8_t** vis, SbDpSync* sync) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    if (!h) { sb_set_error("multi-GPU exchange handle is NULL (sb200_dp_create)"); return 1; }
+    if (P > h->capacity) { sb_set_error("exchange: %d surfels exceed the capacity %lld", P, (long long)h->capacity); return 1; }
+    h->step += 1;   // every rank calls in lockstep: the same number everywhere
+    *stage = (float*)(h->base[h->rank] + h->L.stage);
+    *vis = (uint8_t*)(h->base[h->rank] + h->L.vis);
+    *sync = sb_dp_sync_of(h);
+    return 0;
+}
+
 extern "C" {
 
-size_t sb200_dp_stage_bytes(int64_t P) { return sb_align((size_t)(P > 0 ? P : 0) * SB_DP_STAGE_F * 4); }
-size_t sb200_dp_out_bytes(int64_t slice) { return sb_align((size_t)(slice > 0 ? slice : 0) * SB_DP_OUT_F * 4); }
+size_t sb200_dp_buffer_bytes(int64_t capacity, int n_ranks) {
+    if (n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS) return 0;
+    return sb_dp_layout(capacity, n_ranks).total;
+}
 
-int sb200_dp_stage(int P, const float* d_means3D, const float* d_colors, const float* d_opacity, const float* d_scales,
-                   const float* d_rotations, const float* cur_scores, const int* radii, const float* opacity_raw,
-                   const float* scaling_raw, const float* rotation_raw, float* stage, uint8_t* vis, void* stream) {
+void* sb200_dp_create(int rank, int n_ranks, int64_t capacity, const void* const* peer_bases) {
+    if (n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS || rank < 0 || rank >= n_ranks || capacity < 0 || !peer_bases) {
+        sb_set_error("dp_create: bad rank / rank count / capacity");
+        return nullptr;
+    }
+    SbDpHandle* h = new SbDpHandle();
+    h->rank = rank; h->n_ranks = n_ranks; h->capacity = capacity; h->step = 0;
+    h->L = sb_dp_layout(capacity, n_ranks);
+    for (int q = 0; q < n_ranks; q++) {
+        if (!peer_bases[q]) { sb_set_error("dp_create: NULL buffer of rank %d", q); delete h; return nullptr; }
+        h->base[q] = (char*)peer_bases[q];
+    }
+    return h;
+}
+
+void sb200_dp_destroy(void* handle) { delete (SbDpHandle*)handle; }
+
+int sb200_dp_slice(void* handle, int P) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    return h ? (int)((((P + h->n_ranks - 1) / h->n_ranks) + 255) / 256 * 256) : 0;
+}
+
+int sb200_dp_error(void* handle, void* stream) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    if (!h) return 1;
+    uint32_t e = 0;
+    if (cudaMemcpyAsync(&e, h->base[h->rank] + h->L.error, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream) != cudaSuccess ||
+        cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) { sb_set_error("dp_error: read failed"); return 2; }
+    if (e) { sb_set_error("multi-GPU exchange: a rank waited 20 s for a peer that never signalled"); return 3; }
+    return 0;
+}
+
+int sb200_dp_stage(void* handle, int P, const float* d_means3D, const float* d_colors, const float* d_opacity,
+                   const float* d_scales, const float* d_rotations, const float* cur_scores, const int* radii,
+                   const float* opacity_raw, const float* scaling_raw, const float* rotation_raw, void* stream) {
     if (P < 0) { sb_set_error("dp_stage: bad P"); return 1; }
-    if (P == 0) return 0;
-    if (!d_means3D || !d_colors || !d_opacity || !d_scales || !d_rotations || !cur_scores || !radii || !opacity_raw ||
-        !scaling_raw || !rotation_raw || !stage || !vis) { sb_set_error("dp_stage: NULL input"); return 1; }
+    if (P > 0 && (!d_means3D || !d_colors || !d_opacity || !d_scales || !d_rotations || !cur_scores || !radii ||
+                  !opacity_raw || !scaling_raw || !rotation_raw)) { sb_set_error("dp_stage: NULL input"); return 1; }
     if ((((uintptr_t)d_scales | (uintptr_t)cur_scores | (uintptr_t)scaling_raw) & 7) ||
-        (((uintptr_t)d_rotations | (uintptr_t)rotation_raw | (uintptr_t)stage) & 15)) {
-        sb_set_error("dp_stage: [P,2] arrays must be 8-byte, [P,4] arrays and the stage rows 16-byte aligned");
+        (((uintptr_t)d_rotations | (uintptr_t)rotation_raw) & 15)) {
+        sb_set_error("dp_stage: [P,2] arrays must be 8-byte, [P,4] arrays 16-byte aligned");
         return 1;
     }
     SbDpStageArgs a = {d_means3D, d_colors, d_opacity, d_scales, d_rotations, cur_scores, radii,
-                       opacity_raw, scaling_raw, rotation_raw, stage, vis, P};
+                       opacity_raw, scaling_raw, rotation_raw, nullptr, nullptr, P};
+    if (sb_dp_begin_step(handle, P, &a.stage, &a.vis, &a.sync)) return 1;
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_UPDATE, s);
-    sb_dp_stage_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+    sb_dp_stage_kernel<<<(P + 255) / 256 + (P == 0), 256, 0, s>>>(a);   // at least one CTA: it carries the signal
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 
-int sb200_dp_reduce(int lo, int hi, int n_ranks, const void* const* peer_stage, const void* const* peer_vis,
-                    const int64_t* kf_ids, const float* global_scores, float* out, uint8_t* upd, void* stream) {
-    if (lo < 0 || hi < lo || n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS) { sb_set_error("dp_reduce: bad slice / rank count"); return 1; }
-    if (hi == lo) return 0;
-    if (!peer_stage || !peer_vis || !kf_ids || !global_scores || !out || !upd) { sb_set_error("dp_reduce: NULL input"); return 1; }
+int sb200_dp_reduce(void* handle, int P, const int64_t* kf_ids, const float* global_scores, void* stream) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    if (!h || P < 0 || P > h->capacity) { sb_set_error("dp_reduce: bad handle / P"); return 1; }
+    if (!kf_ids || (P > 0 && !global_scores)) { sb_set_error("dp_reduce: NULL input"); return 1; }
+    const int S = sb200_dp_slice(h, P);
     SbDpReduceArgs a;
-    for (int q = 0; q < n_ranks; q++) {
-        if (!peer_stage[q] || !peer_vis[q]) { sb_set_error("dp_reduce: NULL peer buffer %d", q); return 1; }
-        a.peer_stage[q] = (const float*)peer_stage[q];
-        a.peer_vis[q] = (const uint8_t*)peer_vis[q];
+    memset(&a, 0, sizeof(a));
+    for (int q = 0; q < h->n_ranks; q++) {
+        a.peer_stage[q] = (const float*)(h->base[q] + h->L.stage);
+        a.peer_vis[q] = (const uint8_t*)(h->base[q] + h->L.vis);
         a.kf_ids[q] = kf_ids[q];
     }
-    a.global_scores = global_scores; a.out = out; a.upd = upd; a.lo = lo; a.hi = hi; a.n_ranks = n_ranks;
+    a.global_scores = global_scores;
+    a.out = (float*)(h->base[h->rank] + h->L.out);
+    a.upd = (uint8_t*)(h->base[h->rank] + h->L.upd);
+    a.lo = P < h->rank * S ? P : h->rank * S;
+    a.hi = P < (h->rank + 1) * S ? P : (h->rank + 1) * S;
+    a.n_ranks = h->n_ranks;
+    a.sync = sb_dp_sync_of(h);
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_DP_REDUCE, s);
-    sb_dp_reduce_kernel<<<(hi - lo + 255) / 256, 256, 0, s>>>(a);
+    const int n = a.hi - a.lo;
+    sb_dp_reduce_kernel<<<(n + 255) / 256 + (n == 0), 256, 0, s>>>(a);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
 }
 
-int sb200_dp_post(int P, int slice, int n_ranks, const void* const* peer_out, const void* const* peer_upd,
-                  float* const* params, float* const* exp_avg, float* const* exp_avg_sq, const uint8_t* stable_mask,
-                  float* local_scores, float* global_scores, float* kf_max_scores, int64_t* kf_id, const float* lr,
-                  float b1, float b2, float eps, void* stream) {
-    if (P < 0 || slice < 1 || n_ranks < 1 || n_ranks > SB_DP_MAX_RANKS || (int64_t)slice * n_ranks < P) {
-        sb_set_error("dp_post: bad P / slice / rank count");
+int sb200_dp_post(void* handle, int P, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+                  const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
+                  int64_t* kf_id, const float* lr, float b1, float b2, float eps, void* stream) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    if (!h || P < 0 || P > h->capacity) { sb_set_error("dp_post: bad handle / P"); return 1; }
+    if (!params || !exp_avg || !exp_avg_sq || !lr || (P > 0 && (!stable_mask || !local_scores || !global_scores ||
+                                                                 !kf_max_scores || !kf_id))) {
+        sb_set_error("dp_post: NULL input");
         return 1;
     }
-    if (P == 0) return 0;
-    if (!peer_out || !peer_upd || !params || !exp_avg || !exp_avg_sq || !stable_mask || !local_scores ||
-        !global_scores || !kf_max_scores || !kf_id || !lr) { sb_set_error("dp_post: NULL input"); return 1; }
     if ((((uintptr_t)params[3] | (uintptr_t)exp_avg[3] | (uintptr_t)exp_avg_sq[3]) & 7) ||
         (((uintptr_t)params[4] | (uintptr_t)exp_avg[4] | (uintptr_t)exp_avg_sq[4]) & 15)) {
         sb_set_error("dp_post: scaling arrays must be 8-byte, rotation arrays 16-byte aligned");
         return 1;
     }
     SbDpPostArgs a;
-    for (int q = 0; q < n_ranks; q++) {
-        if (!peer_out[q] || !peer_upd[q]) { sb_set_error("dp_post: NULL peer buffer %d", q); return 1; }
-        a.peer_out[q] = (const float*)peer_out[q];
-        a.peer_upd[q] = (const uint8_t*)peer_upd[q];
+    memset(&a, 0, sizeof(a));
+    for (int q = 0; q < h->n_ranks; q++) {
+        a.peer_out[q] = (const float*)(h->base[q] + h->L.out);
+        a.peer_upd[q] = (const uint8_t*)(h->base[q] + h->L.upd);
     }
     for (int g = 0; g < 5; g++) { a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g]; }
     a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;
-    a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.slice = slice;
+    a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.slice = sb200_dp_slice(h, P);
+    if (a.slice < 1) a.slice = 256;
+    a.sync = sb_dp_sync_of(h);
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_DP_POST, s);
-    sb_dp_post_kernel<<<(P + 255) / 256, 256, 0, s>>>(a);
+    sb_dp_post_kernel<<<(P + 255) / 256 + (P == 0), 256, 0, s>>>(a);
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;

@@ -16,6 +16,7 @@
 //                   fused [16,P] buffer that NCCL reduces;
 //   SB_UPD_DP_POST  bookkeeping + Adam from the reduced buffer.
 #include "prebwd_math.cuh"
+#include "dp_sync.cuh"
 #include <string.h>
 #include "../../include/surfel_b200.h"
 
@@ -240,15 +241,12 @@ struct SbViewUpdateArgs {
     const float* viewmatrix; const float* projmatrix;
     const float* grad_acc;         // [P, SB_GRAD_F] the backward blend's accumulation records
     float* stage; uint8_t* vis;    // MODE 1
+    SbDpSync sync;                 // MODE 1: hand-off to the peers' reduce kernels
     int Wq, Hq;
 };
 
 template <int MODE>
-__global__ void __launch_bounds__(256) sb_view_update_kernel(SbViewUpdateArgs va) {
-    __shared__ float s_vm[16], s_pm[16];
-    if (threadIdx.x < 16) s_vm[threadIdx.x] = va.viewmatrix[threadIdx.x];
-    else if (threadIdx.x < 32) s_pm[threadIdx.x - 16] = va.projmatrix[threadIdx.x - 16];
-    __syncthreads();
+__device__ __forceinline__ void sb_view_update_body(const SbViewUpdateArgs& va, const float* s_vm, const float* s_pm) {
     const SbUpdateArgs& a = va.u;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= a.P) return;
@@ -368,6 +366,18 @@ __global__ void __launch_bounds__(256) sb_view_update_kernel(SbViewUpdateArgs va
     }
 }
 
+template <int MODE>
+__global__ void __launch_bounds__(256) sb_view_update_kernel(SbViewUpdateArgs va) {
+    __shared__ float s_vm[16], s_pm[16];
+    if (threadIdx.x < 16) s_vm[threadIdx.x] = va.viewmatrix[threadIdx.x];
+    else if (threadIdx.x < 32) s_pm[threadIdx.x - 16] = va.projmatrix[threadIdx.x - 16];
+    __syncthreads();
+    sb_view_update_body<MODE>(va, s_vm, s_pm);
+    if (MODE == 1) sb_dp_signal(va.sync, 0);
+}
+
+int sb_dp_begin_step(void* handle, int P, float** stage, uint8_t** vis, SbDpSync* sync);   // dp_exchange.cu
+
 int sb_launch_view_update(int mode, int W, int H, float tanfovx, float tanfovy, SbViewUpdateArgs& va, cudaStream_t s) {
     if (va.u.P == 0) return 0;
     // Q8: the reference re-derives the image size from focal*tan in fp32 (backward.cu:1022-1023)
@@ -393,16 +403,17 @@ extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float
                                      float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
                                      const uint8_t* stable_mask, float* local_scores, float* global_scores,
                                      float* kf_max_scores, int64_t* kf_id, int64_t kf, const float* lr, float b1,
-                                     float b2, float eps, float* stage, uint8_t* vis, void* stream) {
+                                     float b2, float eps, void* dp, void* stream) {
     if (P < 0 || W <= 0 || H <= 0 || (mode != 0 && mode != 1)) { sb_set_error("backward_update: bad P / size / mode"); return 1; }
+    if (P == 0 && mode == 1) { sb_set_error("backward_update: the multi-GPU exchange needs at least one surfel"); return 1; }
     if (P == 0) return 0;
     if (!means3D || !scales || !rotations || !viewmatrix || !projmatrix || !radii || !geom_ws || !image_ws || !grad_ws ||
         !dL_dout_color || !dL_dout_others || !pixel_mask || !params) { sb_set_error("backward_update: NULL input"); return 1; }
     if (mode == 0 && (!exp_avg || !exp_avg_sq || !stable_mask || !local_scores || !global_scores || !kf_max_scores ||
                       !kf_id || !lr)) { sb_set_error("backward_update: NULL update input"); return 1; }
-    if (mode == 1 && (!stage || !vis)) { sb_set_error("backward_update: NULL stage buffers"); return 1; }
-    if ((((uintptr_t)params[3] | (uintptr_t)scales) & 7) || (((uintptr_t)params[4] | (uintptr_t)rotations | (uintptr_t)stage) & 15)) {
-        sb_set_error("backward_update: [P,2] arrays must be 8-byte, [P,4] arrays and stage rows 16-byte aligned");
+    if (mode == 1 && !dp) { sb_set_error("backward_update: mode 1 needs the exchange handle"); return 1; }
+    if ((((uintptr_t)params[3] | (uintptr_t)scales) & 7) || (((uintptr_t)params[4] | (uintptr_t)rotations) & 15)) {
+        sb_set_error("backward_update: [P,2] arrays must be 8-byte, [P,4] arrays 16-byte aligned");
         return 1;
     }
     cudaStream_t s = (cudaStream_t)stream;
@@ -431,7 +442,8 @@ extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float
     va.u.kf_max = kf_max_scores; va.u.kf_id = (long long*)kf_id; va.u.b1 = b1; va.u.b2 = b2; va.u.eps = eps; va.u.kf = kf;
     va.u.P = P; va.u.mode = mode;
     va.means3D = means3D; va.act_scales = scales; va.act_rot = rotations; va.viewmatrix = viewmatrix; va.projmatrix = projmatrix;
-    va.grad_acc = (const float*)grad_ws; va.stage = stage; va.vis = vis;
+    va.grad_acc = (const float*)grad_ws;
+    if (mode == 1 && sb_dp_begin_step(dp, P, &va.stage, &va.vis, &va.sync)) return 1;
     SbStageScope sc(SB200_STAGE_UPDATE, s);
     return sb_launch_view_update(mode, W, H, tanfovx, tanfovy, va, s);
 }

@@ -104,17 +104,23 @@ def _load():
                                         [_f32] * 3 + [_vp])
     lib.sb200_backward_update.restype = _i32
     lib.sb200_backward_update.argtypes = ([_i32, _i32, _i32, _i64, _vp, _f32, _f32] + [_vp] * 15 + [_i32] + [_vp] * 8 +
-                                          [_i64, _vp] + [_f32] * 3 + [_vp] * 3)
-    lib.sb200_dp_stage_bytes.restype = _sz
-    lib.sb200_dp_stage_bytes.argtypes = [_i64]
-    lib.sb200_dp_out_bytes.restype = _sz
-    lib.sb200_dp_out_bytes.argtypes = [_i64]
+                                          [_i64, _vp] + [_f32] * 3 + [_vp] * 2)
+    lib.sb200_dp_buffer_bytes.restype = _sz
+    lib.sb200_dp_buffer_bytes.argtypes = [_i64, _i32]
+    lib.sb200_dp_create.restype = _vp
+    lib.sb200_dp_create.argtypes = [_i32, _i32, _i64, _vp]
+    lib.sb200_dp_destroy.restype = None
+    lib.sb200_dp_destroy.argtypes = [_vp]
+    lib.sb200_dp_slice.restype = _i32
+    lib.sb200_dp_slice.argtypes = [_vp, _i32]
+    lib.sb200_dp_error.restype = _i32
+    lib.sb200_dp_error.argtypes = [_vp, _vp]
     lib.sb200_dp_stage.restype = _i32
-    lib.sb200_dp_stage.argtypes = [_i32] + [_vp] * 13
+    lib.sb200_dp_stage.argtypes = [_vp, _i32] + [_vp] * 11
     lib.sb200_dp_reduce.restype = _i32
-    lib.sb200_dp_reduce.argtypes = [_i32, _i32, _i32] + [_vp] * 7
+    lib.sb200_dp_reduce.argtypes = [_vp, _i32, _vp, _vp, _vp]
     lib.sb200_dp_post.restype = _i32
-    lib.sb200_dp_post.argtypes = [_i32, _i32, _i32] + [_vp] * 11 + [_f32] * 3 + [_vp]
+    lib.sb200_dp_post.argtypes = [_vp, _i32] + [_vp] * 9 + [_f32] * 3 + [_vp]
     lib.sb200_knn_mean_dist2.restype = _i32
     lib.sb200_knn_mean_dist2.argtypes = [_i32, _vp, _vp, _vp]
     lib.sb200_prune_scratch_bytes.restype = _sz

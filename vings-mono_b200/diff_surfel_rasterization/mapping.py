@@ -206,10 +206,10 @@ class RasterWorkspace:
 
 def backward_update(ws, mode, d_color, d_allmap, means3D, scales, rotations, bg, viewmatrix, projmatrix, tanfovx, tanfovy,
                     params, exp_avg, exp_avg_sq, lr, stable_mask, local_scores, global_scores, kf_max_scores, kf_id, kf,
-                    stage=None, vis=None, pixel_mask=None, betas=(0.9, 0.999), eps=1e-15, reuse_records=False):
+                    dp=None, pixel_mask=None, betas=(0.9, 0.999), eps=1e-15, reuse_records=False):
     """sb200_backward_update (include/surfel_b200.h): the rasterizer's backward and the per-surfel update of the
     mapping step as one call, with no dense gradient arrays in between.  mode 0 = single-GPU update, mode 1 = stage
-    rows for the multi-GPU exchange (stage / vis: raw device pointers of the rank's peer-mapped buffers)."""
+    rows + signal of the multi-GPU exchange (dp: the rank's exchange handle, PeerExchange.handle)."""
     lib = _load()
     mask = ws.pixel_mask if pixel_mask is None else pixel_mask
     lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
@@ -221,8 +221,8 @@ def backward_update(ws, mode, d_color, d_allmap, means3D, scales, rotations, bg,
         _ptr(mask), _ptr(ws.grad_ws), int(mode), _ptr_array(params),
         _ptr_array(exp_avg) if exp_avg is not None else null, _ptr_array(exp_avg_sq) if exp_avg_sq is not None else null,
         _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores), _ptr(kf_max_scores), _ptr(kf_id), int(kf), lr_arr,
-        float(betas[0]), float(betas[1]), float(eps), _vp(stage) if stage else null, _vp(vis) if vis else null,
-        _stream(ws.device)), "sb200_backward_update")
+        float(betas[0]), float(betas[1]), float(eps), _vp(dp) if dp else null, _stream(ws.device)),
+        "sb200_backward_update")
 
 
 def _ptr_array(tensors):
@@ -259,8 +259,9 @@ def surfel_update(mode, params, exp_avg, exp_avg_sq, lr, ws, stable_mask, local_
 class PeerExchange:
     """The multi-GPU exchange of one optimizer step as three kernels over NVLink peer memory (csrc/dp_exchange.cu):
     every rank stages the rows of the surfels ITS view saw, reduces the slice of surfels it owns by loading its
-    peers' rows, and every rank then applies bookkeeping + Adam from the owners' result rows.  PyTorch's symmetric
-    memory provides the peer-mapped allocation and the barrier between the kernels; nothing else of it is used."""
+    peers' rows, and every rank then applies bookkeeping + Adam from the owners' result rows.  The kernels hand over to
+    each other through flags inside the peer-mapped buffers; PyTorch's symmetric memory only provides the allocation
+    (one buffer per rank, mapped into every process) -- no barrier and no collective is called per step."""
 
     def __init__(self, capacity, group, device):
         import torch.distributed as dist
@@ -271,80 +272,49 @@ class PeerExchange:
         if self.world > 16:
             raise RuntimeError("PeerExchange supports up to 16 ranks")
         self.capacity, self.device = int(capacity), device
-        N = self.world
-        self.slice_cap = ((self.capacity + N - 1) // N + 255) // 256 * 256
-        a256 = lambda n: (n + 255) // 256 * 256
-        self.off_stage = 0
-        self.off_vis = self.off_stage + lib.sb200_dp_stage_bytes(self.capacity)
-        self.off_out = self.off_vis + a256(self.capacity)
-        self.off_upd = self.off_out + lib.sb200_dp_out_bytes(self.slice_cap)
-        total = self.off_upd + a256(self.slice_cap)
+        total = lib.sb200_dp_buffer_bytes(self.capacity, self.world)
         self.buf = symm_mem.empty(total, dtype=torch.uint8, device=device)
         self.buf.zero_()
         self.hdl = symm_mem.rendezvous(self.buf, self.group)
         bases = [int(p) for p in self.hdl.buffer_ptrs]
-        if len(bases) != N or not all(bases):
+        if len(bases) != self.world or not all(bases):
             raise RuntimeError("symmetric memory rendezvous returned no peer pointers")
-        arr = lambda off: (ctypes.c_void_p * N)(*[b + off for b in bases])
-        self.peer_stage, self.peer_vis = arr(self.off_stage), arr(self.off_vis)
-        self.peer_out, self.peer_upd = arr(self.off_out), arr(self.off_upd)
-        self.local = bases[self.rank]
-        self.timing = None   # set to [] to collect CUDA-event pairs around the two barriers (bench.py, tools/)
+        self.handle = lib.sb200_dp_create(self.rank, self.world, self.capacity, (ctypes.c_void_p * self.world)(*bases))
+        if not self.handle:
+            raise RuntimeError("sb200_dp_create failed: %s" % lib.sb200_last_error().decode())
         torch.cuda.synchronize(device)
-        self.hdl.barrier(channel=0)   # every rank has zeroed its buffer before anyone reads it
+        self.hdl.barrier(channel=0)   # once: every rank has zeroed its buffer (flags included) before anyone signals
 
-    def _barrier(self, channel):
-        """Barrier over the ranks on the current stream (signal pads of the symmetric allocation).  Its device time is
-        the wait for the slowest rank of the step plus the signalling itself."""
-        if self.timing is None:
-            self.hdl.barrier(channel=channel)
-            return
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        self.hdl.barrier(channel=channel)
-        e1.record()
-        self.timing.append((channel, e0, e1))
-
-    def read_timing(self):
-        """{barrier channel: (total ms, count)} since timing was switched on; waits for the events."""
-        out = {}
-        for ch, e0, e1 in self.timing or []:
-            e1.synchronize()
-            ms, n = out.get(ch, (0.0, 0))
-            out[ch] = (ms + e0.elapsed_time(e1), n + 1)
-        self.timing = []
-        return out
+    def __del__(self):
+        try:
+            if getattr(self, "handle", None):
+                _load().sb200_dp_destroy(self.handle)
+                self.handle = None
+        except Exception:
+            pass
 
     def slice_rows(self, P):
-        """Rows per owner for P surfels (the same on every rank: multiple of 256, P <= slice * world)."""
-        return ((P + self.world - 1) // self.world + 255) // 256 * 256
+        """Rows per owner for P surfels (the same on every rank)."""
+        return int(_load().sb200_dp_slice(_vp(self.handle), int(P)))
 
-    def stage_ptrs(self):
-        """(stage rows, visibility bytes) of this rank, for backward_update(mode=1)."""
-        return self.local + self.off_stage, self.local + self.off_vis
+    def check(self):
+        """Raises if a kernel of this rank ever gave up waiting for a peer (synchronises the stream)."""
+        _check(_load().sb200_dp_error(_vp(self.handle), _stream(self.device)), "multi-GPU exchange")
 
     def step(self, ws, params, exp_avg, exp_avg_sq, lr, stable_mask, local_scores, global_scores, kf_max_scores, kf_id,
              kf_ids, betas=(0.9, 0.999), eps=1e-15, staged=False):
-        """staged=True: this view's stage rows were already written by backward_update(mode=1)."""
+        """staged=True: this view's stage rows were already written (and signalled) by backward_update(mode=1)."""
         lib = _load()
         P, dev = params[0].shape[0], self.device
-        if P > self.capacity:
-            raise RuntimeError("PeerExchange: %d surfels exceed the capacity %d" % (P, self.capacity))
         st = _stream(dev)
-        S = self.slice_rows(P)
-        lo, hi = min(P, self.rank * S), min(P, (self.rank + 1) * S)
+        h = _vp(self.handle)
         if not staged:
-            _check(lib.sb200_dp_stage(P, _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
+            _check(lib.sb200_dp_stage(h, P, _ptr(ws.d_means3D), _ptr(ws.d_colors), _ptr(ws.d_opacity), _ptr(ws.d_scales),
                                       _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
-                                      _ptr(params[4]), _vp(self.local + self.off_stage), _vp(self.local + self.off_vis), st),
-                   "sb200_dp_stage")
-        self._barrier(0)
+                                      _ptr(params[4]), st), "sb200_dp_stage")
         kf_arr = (ctypes.c_int64 * self.world)(*[int(k) for k in kf_ids])
-        _check(lib.sb200_dp_reduce(lo, hi, self.world, self.peer_stage, self.peer_vis, kf_arr, _ptr(global_scores),
-                                   _vp(self.local + self.off_out), _vp(self.local + self.off_upd), st), "sb200_dp_reduce")
-        self._barrier(1)
+        _check(lib.sb200_dp_reduce(h, P, kf_arr, _ptr(global_scores), st), "sb200_dp_reduce")
         lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
-        _check(lib.sb200_dp_post(P, S, self.world, self.peer_out, self.peer_upd, _ptr_array(params), _ptr_array(exp_avg),
-                                 _ptr_array(exp_avg_sq), _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores),
-                                 _ptr(kf_max_scores), _ptr(kf_id), lr_arr, float(betas[0]), float(betas[1]), float(eps),
-                                 st), "sb200_dp_post")
+        _check(lib.sb200_dp_post(h, P, _ptr_array(params), _ptr_array(exp_avg), _ptr_array(exp_avg_sq),
+                                 _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores), _ptr(kf_max_scores),
+                                 _ptr(kf_id), lr_arr, float(betas[0]), float(betas[1]), float(eps), st), "sb200_dp_post")

@@ -218,8 +218,8 @@ class SurfelMapper:
     def parallelism(self):
         if self.world_size <= 1:
             return "single GPU"
-        how = ("kernels over NVLink peer memory: stage rows of visible surfels, reduce-scatter by peer loads, "
-               "all-gather fused into the Adam update" if (self.fused and self.exchange == "p2p")
+        how = ("kernels over NVLink peer memory (stage rows of visible surfels, reduce-scatter by peer loads, all-gather "
+               "fused into the Adam update; flag hand-offs between them, no collective call)" if (self.fused and self.exchange == "p2p")
                else "dense [16,P] sum all-reduce + [2,P] max all-reduce (NCCL)" if self.fused
                else "torch: fused [16,P] all-reduce + all-gather of the view scores")
         return "window views partitioned over %d ranks, surfels replicated; exchange = %s" % (self.world_size, how)
@@ -380,8 +380,7 @@ class SurfelMapper:
         common = (d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
                   view["tanfovx"], view["tanfovy"], prm, m, v, lr)
         if self.world_size > 1 and self.exchange == "p2p":
-            stage, vis = self._dpx.stage_ptrs()
-            mp.backward_update(ws, 1, *common, *book, kf_id, stage=stage, vis=vis, eps=eps)
+            mp.backward_update(ws, 1, *common, *book, kf_id, dp=self._dpx.handle, eps=eps)
             self._dpx.step(ws, prm, m, v, lr, *book, self._all_kf_ids(kf_id, kf_ids), eps=eps, staged=True)
         elif self.world_size > 1:
             ws.backward(d_color, d_allmap, prm[0], scales, rot, self.bg, view["viewmatrix"], view["projmatrix"],
