@@ -107,33 +107,48 @@ struct SbDpReduceArgs {
     SbDpSync sync;
 };
 
+// Rows that live on another GPU are fetched the way NVLink likes them: the CTA's 256 consecutive rows are one
+// contiguous 16 KB (stage) / 20 KB (result) span, loaded with fully coalesced 512-byte warp requests into shared memory
+// and only then picked apart per thread.  (Per-thread row loads -- 16-byte pieces at a 64 / 80-byte stride -- ran the
+// 2-GPU post kernel at ~110 GB/s of NVLink reads: 0.26 ms for 29 MB.)
 __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
-    const int i = a.lo + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.hi) return;
-    const size_t iz = (size_t)i;
-    const float glob0 = a.global_scores[2 * iz];
+    __shared__ float4 s_rows[256 * (SB_DP_STAGE_F / 4)];
+    const int i0 = a.lo + blockIdx.x * blockDim.x;       // first surfel of this CTA (lo and the slice are multiples of 256)
+    const int i = i0 + threadIdx.x;
+    const bool mine = i < a.hi;
+    const size_t iz = (size_t)(mine ? i : a.lo);
+    const float glob0 = mine ? a.global_scores[2 * iz] : 0.0f;
     float acc[13];
 #pragma unroll
     for (int c = 0; c < 13; c++) acc[c] = 0.0f;
     float s0_sum = 0.0f, s1_max = 0.0f, s0_max = -1.0f;
     long long kf_arg = 0;
     bool any = false;
+    const int rows = min(256, a.hi - i0);                // rows of this CTA inside the slice (> 0)
     for (int q = 0; q < a.n_ranks; q++) {   // rank order = the order a single process would take the views in
-        if (!sb_ld_peer_u8(a.peer_vis[q] + iz)) continue;
-        const float4* row = (const float4*)(a.peer_stage[q] + iz * SB_DP_STAGE_F);
-        const float4 r0 = sb_ld_peer_f4(row), r1 = sb_ld_peer_f4(row + 1), r2 = sb_ld_peer_f4(row + 2), r3 = sb_ld_peer_f4(row + 3);
-        const float c0 = r3.y, c1 = r3.z;
-        // weighting_grad with this view's score counted into the global score (add_records runs first), as in the
-        // single-GPU pass; the global score itself is updated once, from the sum, by sb_dp_post_kernel
-        const float gw = c0 / (fminf(fmaxf(glob0 + c0, 0.0f), 1e4f) + 1e-6f + c0);
-        const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
+        const bool vis = mine && sb_ld_peer_u8(a.peer_vis[q] + iz) != 0;
+        if (!__syncthreads_or(vis)) continue;            // rank q's view saw none of these 256 surfels
+        const float4* src = (const float4*)(a.peer_stage[q] + (size_t)i0 * SB_DP_STAGE_F);
+        for (int k = threadIdx.x; k < rows * (SB_DP_STAGE_F / 4); k += 256) s_rows[k] = sb_ld_peer_f4(src + k);
+        __syncthreads();
+        if (vis) {
+            const float4* row = s_rows + threadIdx.x * (SB_DP_STAGE_F / 4);
+            const float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
+            const float c0 = r3.y, c1 = r3.z;
+            // weighting_grad with this view's score counted into the global score (add_records runs first), as in the
+            // single-GPU pass; the global score itself is updated once, from the sum, by sb_dp_post_kernel
+            const float gw = c0 / (fminf(fmaxf(glob0 + c0, 0.0f), 1e4f) + 1e-6f + c0);
+            const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
 #pragma unroll
-        for (int c = 0; c < 13; c++) acc[c] = __fadd_rn(acc[c], __fmul_rn(g[c], gw));   // a plain sum of the views' weighted rows
-        s0_sum += c0;
-        s1_max = fmaxf(s1_max, c1);
-        if (c0 > s0_max) { s0_max = c0; kf_arg = a.kf_ids[q]; }   // strict: the first view holding the maximum keeps it
-        any = true;
+            for (int c = 0; c < 13; c++) acc[c] = __fadd_rn(acc[c], __fmul_rn(g[c], gw));   // a plain sum of the views' weighted rows
+            s0_sum += c0;
+            s1_max = fmaxf(s1_max, c1);
+            if (c0 > s0_max) { s0_max = c0; kf_arg = a.kf_ids[q]; }   // strict: the first view holding the maximum keeps it
+            any = true;
+        }
+        __syncthreads();                                 // s_rows is reused for the next rank
     }
+    if (!mine) return;
     const int li = i - a.lo;
     a.upd[li] = any ? 1 : 0;
     if (!any) return;
@@ -162,14 +177,24 @@ struct SbDpPostArgs {
 #define SB_GRP_C0(g) ((g) == 0 ? 0 : (g) == 1 ? 3 : (g) == 2 ? 6 : (g) == 3 ? 7 : 9)
 
 __device__ __forceinline__ void sb_dp_post_body(const SbDpPostArgs& a) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= a.P) return;
-    const size_t iz = (size_t)i;
-    const int owner = i / a.slice, li = i - owner * a.slice;
-    if (!sb_ld_peer_u8(a.peer_upd[owner] + li)) return;   // no view saw it: add_records with zero scores is the identity
-    const float4* o = (const float4*)(a.peer_out[owner] + (size_t)li * SB_DP_OUT_F);
-    const float4 r0 = sb_ld_peer_f4(o), r1 = sb_ld_peer_f4(o + 1), r2 = sb_ld_peer_f4(o + 2), r3 = sb_ld_peer_f4(o + 3),
-                 r4 = sb_ld_peer_f4(o + 4);
+    __shared__ float4 s_rows[256 * (SB_DP_OUT_F / 4)];
+    const int i0 = blockIdx.x * blockDim.x;              // 256 consecutive surfels: one owner (the slice is a multiple of 256)
+    const int i = i0 + threadIdx.x;
+    const bool inside = i < a.P;
+    const size_t iz = (size_t)(inside ? i : 0);
+    const int owner = i0 / a.slice, l0 = i0 - owner * a.slice;
+    // no view saw the surfel: add_records with zero scores is the identity and Adam is masked out
+    const bool touched = inside && sb_ld_peer_u8(a.peer_upd[owner] + l0 + threadIdx.x) != 0;
+    if (!__syncthreads_or(touched)) return;
+    {
+        const int rows = min(256, a.P - i0);
+        const float4* src = (const float4*)(a.peer_out[owner] + (size_t)l0 * SB_DP_OUT_F);
+        for (int k = threadIdx.x; k < rows * (SB_DP_OUT_F / 4); k += 256) s_rows[k] = sb_ld_peer_f4(src + k);
+    }
+    __syncthreads();
+    if (!touched) return;
+    const float4* o = s_rows + threadIdx.x * (SB_DP_OUT_F / 4);
+    const float4 r0 = o[0], r1 = o[1], r2 = o[2], r3 = o[3], r4 = o[4];
     const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
     const float s0_sum = r3.y, s1_max = r3.z, s0_max = r3.w;
     const long long kf_arg = ((long long)__float_as_int(r4.y) << 32) | (unsigned int)__float_as_int(r4.x);
