@@ -233,6 +233,8 @@ class Workload:
 
     def ids(self, s, i):
         """Window view of every rank at view slot i of step s (rank order) -- also the keyframe ids of the step."""
+        if os.environ.get("SB200_BENCH_SAME_VIEW"):   # diagnostic only (invalid as a bench line): no rank skew
+            return [(s * VIEWS_PER_STEP + i) % self.K] * self.world
         return [(s * VIEWS_PER_STEP + i + q) % self.K for q in range(self.world)]
 
     @torch.no_grad()
@@ -405,6 +407,7 @@ def run(emit):
     # (two event records per stage cost ~1.5 % of a view, so they stay out of the pass `value` is taken from)
     R_seen = []
     stage_ms = {}
+    dp_wait = None
     if mine:
         orig_train = mapper.train_view
 
@@ -415,9 +418,16 @@ def run(emit):
         mapper.train_view = train_and_count
         mod.profile_enable(True)
         mod.profile_read()
+        dpx = getattr(mapper, "_dpx", None)
+        if dpx is not None:
+            dpx.wait_ms()
         timed(step_resident, args.steps, args.warmup)
         stage_ms = mod.profile_read()
         mod.profile_enable(False)
+        if dpx is not None:
+            w = dpx.wait_ms()
+            n_views = VIEWS_PER_STEP * (args.steps + args.warmup)
+            dp_wait = {"before_reduce": w[0] / n_views, "before_post": w[1] / n_views}
         mapper.train_view = orig_train
     R_timed = R_seen
     ms_e2e, _, t2 = timed(step_e2e, args.steps, args.warmup)
@@ -457,6 +467,10 @@ def run(emit):
         out["churn"] = {"surfels_per_timed_step": P_timed, "prune_frac": CHURN_PRUNE_FRAC, "added_per_step": CHURN_ADD}
     if same_bits is not None:
         out["replicas_bit_identical"] = same_bits   # parameters, moments, score bookkeeping after the timed steps
+    if dp_wait:
+        # ms per view rank 0's reduce / post kernels spent WAITING for the slowest peer (rank skew), included in the
+        # dp_reduce / dp_post stage times
+        out["dp_wait_ms_per_view"] = dp_wait
     if args.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": "views/s", "cores": os.cpu_count(), "kind": "reference",

@@ -253,6 +253,9 @@ void* sb200_dp_create(int rank, int n_ranks, int64_t capacity, const void* const
 void sb200_dp_destroy(void* handle);
 int sb200_dp_slice(void* handle, int P);
 int sb200_dp_error(void* handle, void* stream);
+/* diagnostics: nanoseconds the first CTA of this rank's reduce ([0]) and post ([1]) kernels spent waiting for the
+ * slowest peer since the last call (i.e. rank skew, not work); resets the counters; synchronises the stream. */
+int sb200_dp_wait_ns(void* handle, uint64_t out[2], void* stream);
 int sb200_dp_stage(void* handle, int P, const float* d_means3D, const float* d_colors, const float* d_opacity,
                    const float* d_scales, const float* d_rotations, const float* cur_scores, const int* radii,
                    const float* opacity_raw, const float* scaling_raw, const float* rotation_raw, void* stream);

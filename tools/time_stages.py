@@ -13,7 +13,7 @@ import util
 
 def main():
     name = sys.argv[1] if len(sys.argv) > 1 else "C2"
-    rounds = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    rounds = int(sys.argv[2]) if len(sys.argv) > 2 and sys.argv[2].isdigit() else 3
     scene, views = synthetic.make_scene(name)
     mine = util.load_mine()
     gc, ga = synthetic.upstream_grads(scene["W"], scene["H"], synthetic.CONFIGS[name]["seed"])
@@ -34,6 +34,14 @@ def main():
             out.append("%s %.4f" % (k, ms / n))
             tot += ms / n
     print(os.environ.get("SB200_LIB", "default").split("/")[-1], "|", " ".join(out), "| sum %.4f" % tot)
+    if "--per-view" in sys.argv:   # how much the window's views differ (rank skew of the multi-GPU step)
+        for vi, inp in enumerate(inps):
+            mine.profile_read()
+            for _ in range(rounds):
+                util.run_impl(mine, inp, gc, ga)
+            st = mine.profile_read()
+            print("view %d: R %d  sum %.4f ms  (fwd %.4f bwd %.4f)" % (vi, mine.last_counters["R"], sum(ms / n for ms, n in st.values() if n),
+                                                                      st["blend_fwd"][0] / st["blend_fwd"][1], st["blend_bwd"][0] / st["blend_bwd"][1]))
 
 
 if __name__ == "__main__":

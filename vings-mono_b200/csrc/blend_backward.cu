@@ -87,10 +87,15 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
     return n_real >= 1 ? base : -1;
 }
 
-#ifndef BB_MIN_CTAS
-#define BB_MIN_CTAS 3  // 80 registers (~100 B of spills) for 24 warps per SM: measured 7 % faster than 2 CTAs at 121
+// Occupancy against spills (measured): 3 CTAs/SM = 80 registers with ~70 B of spills, 4 CTAs/SM =
+// 64 registers with ~170 B.  On the KITTI-shaped image (1872 tiles) 3 is 5 % faster, on the 1080p-class images
+// (8160 / 9600 tiles, deep lists) 4 is 7-9 % faster; 2 CTAs/SM (112 registers, no spills) loses everywhere.  Both are
+// instantiated and the launcher picks by tile count.
+#ifndef BB_DEEP_TILES
+#define BB_DEEP_TILES 4000
 #endif
-__global__ void __launch_bounds__(BB_THREADS, BB_MIN_CTAS)
+template <int MIN_CTAS>
+__global__ void __launch_bounds__(BB_THREADS, MIN_CTAS)
 sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                          const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                          const float* __restrict__ bg, const float* __restrict__ final_T,
@@ -398,7 +403,8 @@ int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, co
                              float* grad_acc, const uint32_t* hit_masks, const uint32_t* walk_cap, cudaStream_t s) {
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
-    sb_blend_backward_kernel<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
+    auto kern = grid_x * grid_y >= BB_DEEP_TILES ? sb_blend_backward_kernel<4> : sb_blend_backward_kernel<3>;
+    kern<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
         dL_dcolor, dL_dothers, pixel_mask, grad_acc, hit_masks, walk_cap);

@@ -24,6 +24,9 @@
 #define FB_WARPS 8
 #define FB_BATCH 32
 #define FB_STAGES 8
+#ifndef FB_POLL_NS
+#define FB_POLL_NS 0
+#endif
 
 // (a min-CTAs bound of 4/5/6 -> 56/48/40 registers was measured 2-5 % slower than the unconstrained 58)
 __global__ void __launch_bounds__(FB_THREADS)
@@ -99,6 +102,9 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         bool stop = false;
         while (!bb_mbar_try(&s_full[st], (uint32_t)(b / FB_STAGES) & 1u)) {
             if (b >= *(volatile int*)&s_limit) { stop = true; break; }
+#if FB_POLL_NS > 0
+            __nanosleep(FB_POLL_NS);   // a warp that is ahead of its CTA should not spend issue slots on probing
+#endif
         }
         if (stop) break;
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);

@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
 }
 
 // ---- host side: one exchange handle per rank (layout of the peer-mapped buffer, peer pointers, step counter) ----
-struct SbDpLayout { size_t stage, vis, out, upd, flags, counter, error, total; int64_t slice_cap; };
+struct SbDpLayout { size_t stage, vis, out, upd, flags, counter, error, wait, total; int64_t slice_cap; };
 static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
     SbDpLayout L;
     const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
@@ -280,6 +280,7 @@ static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
     L.flags = o;   o = sb_align(o + 2 * SB_DP_MAX_RANKS * 4);
     L.counter = o; o = sb_align(o + 2 * 4);
     L.error = o;   o = sb_align(o + 4);
+    L.wait = o;    o = sb_align(o + 2 * 8);
     L.total = o;
     return L;
 }
@@ -298,6 +299,7 @@ static SbDpSync sb_dp_sync_of(const SbDpHandle* h) {
     for (int q = 0; q < h->n_ranks; q++) y.peer_flags[q] = (uint32_t*)(h->base[q] + h->L.flags);
     y.counter = (uint32_t*)(h->base[h->rank] + h->L.counter);
     y.error = (uint32_t*)(h->base[h->rank] + h->L.error);
+    y.wait_ns = (unsigned long long*)(h->base[h->rank] + h->L.wait);
     y.step = h->step;
     y.rank = h->rank;
     y.n_ranks = h->n_ranks;
@@ -352,6 +354,16 @@ int sb200_dp_error(void* handle, void* stream) {
     if (cudaMemcpyAsync(&e, h->base[h->rank] + h->L.error, 4, cudaMemcpyDeviceToHost, (cudaStream_t)stream) != cudaSuccess ||
         cudaStreamSynchronize((cudaStream_t)stream) != cudaSuccess) { sb_set_error("dp_error: read failed"); return 2; }
     if (e) { sb_set_error("multi-GPU exchange: a rank waited 20 s for a peer that never signalled"); return 3; }
+    return 0;
+}
+
+int sb200_dp_wait_ns(void* handle, uint64_t out[2], void* stream) {
+    SbDpHandle* h = (SbDpHandle*)handle;
+    if (!h || !out) return 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (cudaMemcpyAsync(out, h->base[h->rank] + h->L.wait, 16, cudaMemcpyDeviceToHost, s) != cudaSuccess ||
+        cudaMemsetAsync(h->base[h->rank] + h->L.wait, 0, 16, s) != cudaSuccess ||
+        cudaStreamSynchronize(s) != cudaSuccess) { sb_set_error("dp_wait_ns: read failed"); return 2; }
     return 0;
 }
 

@@ -10,6 +10,7 @@ struct SbDpSync {
     uint32_t* peer_flags[SB_DP_MAX_RANKS];   // rank q's flag block u32[2][SB_DP_MAX_RANKS]: [channel][source rank]
     uint32_t* counter;                       // local u32[2]: finished CTAs of the signalling kernel, per channel
     uint32_t* error;                         // local u32: a wait gave up (peer gone)
+    unsigned long long* wait_ns;             // local u64[2]: time CTA 0 spent waiting, per channel (diagnostics)
     uint32_t step;                           // number of this exchange step (increasing, wraps)
     int rank, n_ranks;                       // n_ranks <= 1: nothing to synchronise
 };
@@ -37,6 +38,8 @@ __device__ __forceinline__ void sb_dp_signal(const SbDpSync& y, int ch) {
 // Start of a consuming kernel (ALL threads call it): wait until every peer has signalled step `step` on channel ch.
 __device__ __forceinline__ void sb_dp_wait(const SbDpSync& y, int ch) {
     if (y.n_ranks <= 1) return;
+    unsigned long long w0 = 0;
+    if (blockIdx.x == 0 && threadIdx.x == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(w0));
     if ((int)threadIdx.x < y.n_ranks && (int)threadIdx.x != y.rank) {
         const uint32_t* f = y.peer_flags[y.rank] + ch * SB_DP_MAX_RANKS + threadIdx.x;
         unsigned long long t0 = 0;
@@ -53,5 +56,10 @@ __device__ __forceinline__ void sb_dp_wait(const SbDpSync& y, int ch) {
         }
     }
     __syncthreads();
+    if (blockIdx.x == 0 && threadIdx.x == 0) {   // how long the first CTA waited for the slowest peer (rank skew)
+        unsigned long long w1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(w1));
+        y.wait_ns[ch] += w1 - w0;
+    }
 }
 

@@ -115,6 +115,8 @@ def _load():
     lib.sb200_dp_slice.argtypes = [_vp, _i32]
     lib.sb200_dp_error.restype = _i32
     lib.sb200_dp_error.argtypes = [_vp, _vp]
+    lib.sb200_dp_wait_ns.restype = _i32
+    lib.sb200_dp_wait_ns.argtypes = [_vp, ctypes.POINTER(ctypes.c_uint64), _vp]
     lib.sb200_dp_stage.restype = _i32
     lib.sb200_dp_stage.argtypes = [_vp, _i32] + [_vp] * 11
     lib.sb200_dp_reduce.restype = _i32

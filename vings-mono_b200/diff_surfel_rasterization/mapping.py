@@ -297,6 +297,12 @@ class PeerExchange:
         """Rows per owner for P surfels (the same on every rank)."""
         return int(_load().sb200_dp_slice(_vp(self.handle), int(P)))
 
+    def wait_ms(self):
+        """(ms waited before reduce, ms waited before post) by this rank's first CTAs since the last call: rank skew."""
+        out = (ctypes.c_uint64 * 2)()
+        _check(_load().sb200_dp_wait_ns(_vp(self.handle), out, _stream(self.device)), "sb200_dp_wait_ns")
+        return out[0] * 1e-6, out[1] * 1e-6
+
     def check(self):
         """Raises if a kernel of this rank ever gave up waiting for a peer (synchronises the stream)."""
         _check(_load().sb200_dp_error(_vp(self.handle), _stream(self.device)), "multi-GPU exchange")
