@@ -240,10 +240,11 @@ int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float
  *                     accumulation records.)
  *   sb200_dp_reduce : waits for every peer's stage; for the owned surfels loads the stage rows of every rank that saw
  *                     them, applies weighting_grad per view (scripts/gaussian/gaussian_utils.py:56-62) and folds the
- *                     views in rank order: gradient sum, score-0 sum, score-1 max, first arg-max of score 0 with its
- *                     keyframe id kf_ids[q] (HOST array, one id per rank) -> the owner's result row (20 floats); signals.
+ *                     views in rank order: gradient sum, score-0 sum, score-1 max, score-0 max -> the owner's result row
+ *                     (16 floats); the rank of the first arg-max of score 0 rides in the touched byte; signals.
  *   sb200_dp_post   : waits for every peer's reduce; every rank, every surfel some view saw: loads the owner's result
- *                     row, applies add_records (scripts/gaussian/gaussian_model.py:163-168) for the folded views and the
+ *                     row, applies add_records (scripts/gaussian/gaussian_model.py:163-168) for the folded views (keyframe
+ *                     id of the arg-max view = kf_ids[rank], a HOST array with one id per rank) and the
  *                     masked Adam step (cuda_rasterizer/adam.cu:9-38) to the local replica.  All ranks read the same
  *                     bytes: the replicas stay bit-identical, and equal a single process taking the views in rank order.
  *   sb200_dp_error  : non-zero if a wait ever gave up (a peer did not signal within 20 s); synchronises the stream.
@@ -259,8 +260,8 @@ int sb200_dp_wait_ns(void* handle, uint64_t out[2], void* stream);
 int sb200_dp_stage(void* handle, int P, const float* d_means3D, const float* d_colors, const float* d_opacity,
                    const float* d_scales, const float* d_rotations, const float* cur_scores, const int* radii,
                    const float* opacity_raw, const float* scaling_raw, const float* rotation_raw, void* stream);
-int sb200_dp_reduce(void* handle, int P, const int64_t* kf_ids, const float* global_scores, void* stream);
-int sb200_dp_post(void* handle, int P, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+int sb200_dp_reduce(void* handle, int P, const float* global_scores, void* stream);
+int sb200_dp_post(void* handle, int P, const int64_t* kf_ids, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
                   const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
                   int64_t* kf_id, const float* lr, float b1, float b2, float eps, void* stream);
 

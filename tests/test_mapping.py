@@ -335,10 +335,10 @@ def test_peer_exchange_kernels_equal_the_batched_step_on_one_device():
                                   vp(prm[3].data_ptr()), vp(prm[4].data_ptr()), st_) == 0, lib.sb200_last_error()
     kf_arr = (ctypes.c_int64 * N)(*kf_ids)
     for r in range(N):
-        assert lib.sb200_dp_reduce(vp(handles[r]), P, kf_arr, vp(ba[1].data_ptr()), st_) == 0, lib.sb200_last_error()
+        assert lib.sb200_dp_reduce(vp(handles[r]), P, vp(ba[1].data_ptr()), st_) == 0, lib.sb200_last_error()
     arr5 = lambda ts: (vp * 5)(*[t.data_ptr() for t in ts])
     # rank 0's replica is updated; the other "ranks" would do the same from the same result rows
-    assert lib.sb200_dp_post(vp(handles[0]), P, arr5(pa), arr5(ma), arr5(va), vp(stable.data_ptr()),
+    assert lib.sb200_dp_post(vp(handles[0]), P, kf_arr, arr5(pa), arr5(ma), arr5(va), vp(stable.data_ptr()),
                              vp(ba[0].data_ptr()), vp(ba[1].data_ptr()), vp(ba[2].data_ptr()), vp(ba[3].data_ptr()),
                              (ctypes.c_float * 5)(*lr), 0.9, 0.999, 1e-15, st_) == 0, lib.sb200_last_error()
     torch.cuda.synchronize()

@@ -18,13 +18,14 @@
 //   sb_dp_reduce_kernel  (rank r, its slice of the surfels)   a reduce-scatter by peer LOADS: for the surfels it
 //                        owns the rank reads the stage rows of the ranks that saw them, applies weighting_grad per
 //                        view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views IN RANK ORDER into one
-//                        80-B result row: gradient sum, add_records' running quantities (gaussian_model.py:163-168:
-//                        score sum, max of the second score, first arg-max of the first score and its keyframe id).
+//                        64-B result row: gradient sum, add_records' running quantities (gaussian_model.py:163-168:
+//                        score sum, max of the second score, max of the first score; the rank of its first arg-max
+//                        rides in the touched byte).
 //   -- same hand-off on a second flag channel --
 //   sb_dp_post_kernel    (every rank, all surfels)   an all-gather fused with its consumer: reads the result row of
 //                        every touched surfel from its owner (peer load for 7/8 of them) and applies the score
 //                        bookkeeping and the masked Adam step to the local replica.  Every rank consumes the same
-//                        80 bytes, so the replicas stay bit-identical by construction.
+//                        65 bytes, so the replicas stay bit-identical by construction.
 //
 // There is no barrier kernel and no collective call: the only cross-GPU synchronisation is those two flag hand-offs
 // (monotonic step counters, never reset), and they also order the buffers' reuse -- a rank's next stage kernel
@@ -38,7 +39,8 @@
 #include "../../include/surfel_b200.h"
 
 #define SB_DP_STAGE_F 16   // floats per stage row: 13 gradients, score 0, score 1, pad
-#define SB_DP_OUT_F 20     // floats per result row: 13 gradients, score sum, score-1 max, score-0 max, kf id (2 words), pad 2
+#define SB_DP_OUT_F 16     // floats per result row: 13 gradients, score-0 sum, score-1 max, score-0 max; the rank whose view
+                           // holds that maximum travels in the `upd` byte (1 + rank; 0 = no view saw the surfel)
 
 // Loads of rows another GPU wrote: the writer's kernel released them with a system-scope store of the step number,
 // this kernel acquired that flag (sb_dp_wait) before any thread gets here, so ordinary loads observe them; .cg keeps
@@ -99,7 +101,6 @@ __device__ __forceinline__ void sb_dp_stage_body(const SbDpStageArgs& a) {
 struct SbDpReduceArgs {
     const float* peer_stage[SB_DP_MAX_RANKS];
     const uint8_t* peer_vis[SB_DP_MAX_RANKS];
-    long long kf_ids[SB_DP_MAX_RANKS];
     const float* global_scores;   // [P,2] local replica (identical on every rank)
     float* out;                   // [slice, SB_DP_OUT_F] this rank's result rows
     uint8_t* upd;                 // [slice] 1 = some view saw the surfel
@@ -112,27 +113,44 @@ struct SbDpReduceArgs {
 // and only then picked apart per thread.  (Per-thread row loads -- 16-byte pieces at a 64 / 80-byte stride -- ran the
 // 2-GPU post kernel at ~110 GB/s of NVLink reads: 0.26 ms for 29 MB.)
 __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
-    __shared__ float4 s_rows[256 * (SB_DP_STAGE_F / 4)];
+    __shared__ float4 s_rows[2][256 * (SB_DP_STAGE_F / 4)];   // double buffered: the next rank's span arrives while this one is folded
+    __shared__ uint32_t s_any;                                // bit q: rank q's view saw one of this CTA's surfels
     const int i0 = a.lo + blockIdx.x * blockDim.x;       // first surfel of this CTA (lo and the slice are multiples of 256)
     const int i = i0 + threadIdx.x;
     const bool mine = i < a.hi;
     const size_t iz = (size_t)(mine ? i : a.lo);
+    const int rows = min(256, a.hi - i0);                // rows of this CTA inside the slice
+    // every rank's visibility byte first: n_ranks independent peer loads in flight, not a chain of them
+    uint32_t vis_bits = 0;
+    if (threadIdx.x == 0) s_any = 0;
+    __syncthreads();
+    if (mine) {
+#pragma unroll 4
+        for (int q = 0; q < a.n_ranks; q++) vis_bits |= (sb_ld_peer_u8(a.peer_vis[q] + iz) != 0 ? 1u : 0u) << q;
+    }
+    const uint32_t warp_bits = __reduce_or_sync(0xffffffffu, vis_bits);
+    if ((threadIdx.x & 31) == 0 && warp_bits) atomicOr(&s_any, warp_bits);
     const float glob0 = mine ? a.global_scores[2 * iz] : 0.0f;
+    __syncthreads();
+    uint32_t todo = s_any;
     float acc[13];
 #pragma unroll
     for (int c = 0; c < 13; c++) acc[c] = 0.0f;
     float s0_sum = 0.0f, s1_max = 0.0f, s0_max = -1.0f;
-    long long kf_arg = 0;
-    bool any = false;
-    const int rows = min(256, a.hi - i0);                // rows of this CTA inside the slice (> 0)
-    for (int q = 0; q < a.n_ranks; q++) {   // rank order = the order a single process would take the views in
-        const bool vis = mine && sb_ld_peer_u8(a.peer_vis[q] + iz) != 0;
-        if (!__syncthreads_or(vis)) continue;            // rank q's view saw none of these 256 surfels
+    int arg_rank = 0;
+    auto fetch = [&](int q, int buf) {   // the CTA's 16-KB span of rank q's stage rows, coalesced 512-byte requests
         const float4* src = (const float4*)(a.peer_stage[q] + (size_t)i0 * SB_DP_STAGE_F);
-        for (int k = threadIdx.x; k < rows * (SB_DP_STAGE_F / 4); k += 256) s_rows[k] = sb_ld_peer_f4(src + k);
-        __syncthreads();
-        if (vis) {
-            const float4* row = s_rows + threadIdx.x * (SB_DP_STAGE_F / 4);
+        for (int k = threadIdx.x; k < rows * (SB_DP_STAGE_F / 4); k += 256) s_rows[buf][k] = sb_ld_peer_f4(src + k);
+    };
+    int buf = 0;
+    if (todo) fetch(__ffs(todo) - 1, 0);
+    while (todo) {   // ascending q = rank order = the order a single process would take the views in
+        const int q = __ffs(todo) - 1;
+        todo &= todo - 1;
+        __syncthreads();                                  // span q has landed (and the other buffer is free again)
+        if (todo) fetch(__ffs(todo) - 1, buf ^ 1);
+        if ((vis_bits >> q) & 1u) {
+            const float4* row = s_rows[buf] + threadIdx.x * (SB_DP_STAGE_F / 4);
             const float4 r0 = row[0], r1 = row[1], r2 = row[2], r3 = row[3];
             const float c0 = r3.y, c1 = r3.z;
             // weighting_grad with this view's score counted into the global score (add_records runs first), as in the
@@ -143,21 +161,19 @@ __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
             for (int c = 0; c < 13; c++) acc[c] = __fadd_rn(acc[c], __fmul_rn(g[c], gw));   // a plain sum of the views' weighted rows
             s0_sum += c0;
             s1_max = fmaxf(s1_max, c1);
-            if (c0 > s0_max) { s0_max = c0; kf_arg = a.kf_ids[q]; }   // strict: the first view holding the maximum keeps it
-            any = true;
+            if (c0 > s0_max) { s0_max = c0; arg_rank = q; }   // strict: the first view holding the maximum keeps it
         }
-        __syncthreads();                                 // s_rows is reused for the next rank
+        buf ^= 1;
     }
     if (!mine) return;
     const int li = i - a.lo;
-    a.upd[li] = any ? 1 : 0;
-    if (!any) return;
+    a.upd[li] = vis_bits ? (uint8_t)(1 + arg_rank) : 0;
+    if (!vis_bits) return;
     float4* o = (float4*)(a.out + (size_t)li * SB_DP_OUT_F);
     o[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
     o[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
     o[2] = make_float4(acc[8], acc[9], acc[10], acc[11]);
     o[3] = make_float4(acc[12], s0_sum, s1_max, s0_max);
-    o[4] = make_float4(__int_as_float((int)(kf_arg & 0xffffffffll)), __int_as_float((int)(kf_arg >> 32)), 0.0f, 0.0f);
 }
 
 struct SbDpPostArgs {
@@ -168,6 +184,7 @@ struct SbDpPostArgs {
     float* local_scores; float* global_scores; float* kf_max; long long* kf_id;
     float lr[5];
     float b1, b2, eps;
+    long long kf_ids[SB_DP_MAX_RANKS];   // keyframe id of every rank's view of this step
     int P, slice;
     SbDpSync sync;
 };
@@ -183,21 +200,22 @@ __device__ __forceinline__ void sb_dp_post_body(const SbDpPostArgs& a) {
     const bool inside = i < a.P;
     const size_t iz = (size_t)(inside ? i : 0);
     const int owner = i0 / a.slice, l0 = i0 - owner * a.slice;
-    // no view saw the surfel: add_records with zero scores is the identity and Adam is masked out
-    const bool touched = inside && sb_ld_peer_u8(a.peer_upd[owner] + l0 + threadIdx.x) != 0;
-    if (!__syncthreads_or(touched)) return;
+    // The owner's touched byte and its span of result rows are requested together (one peer round trip, not two); the
+    // span of a CTA nobody touched is fetched for nothing, which costs NVLink bytes but no latency.
+    const uint32_t ub = inside ? sb_ld_peer_u8(a.peer_upd[owner] + l0 + threadIdx.x) : 0u;
     {
         const int rows = min(256, a.P - i0);
         const float4* src = (const float4*)(a.peer_out[owner] + (size_t)l0 * SB_DP_OUT_F);
         for (int k = threadIdx.x; k < rows * (SB_DP_OUT_F / 4); k += 256) s_rows[k] = sb_ld_peer_f4(src + k);
     }
     __syncthreads();
-    if (!touched) return;
+    // no view saw the surfel: add_records with zero scores is the identity and Adam is masked out
+    if (ub == 0) return;
     const float4* o = s_rows + threadIdx.x * (SB_DP_OUT_F / 4);
-    const float4 r0 = o[0], r1 = o[1], r2 = o[2], r3 = o[3], r4 = o[4];
+    const float4 r0 = o[0], r1 = o[1], r2 = o[2], r3 = o[3];
     const float g[13] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z, r2.w, r3.x};
     const float s0_sum = r3.y, s1_max = r3.z, s0_max = r3.w;
-    const long long kf_arg = ((long long)__float_as_int(r4.y) << 32) | (unsigned int)__float_as_int(r4.x);
+    const long long kf_arg = a.kf_ids[ub - 1];   // the first view (in rank order) holding the score maximum
     const bool adam = !a.stable[i];
 
     // ---- every load before the first store (see sb_surfel_update_kernel) ----
@@ -261,7 +279,7 @@ __global__ void __launch_bounds__(256) sb_dp_reduce_kernel(SbDpReduceArgs a) {
     sb_dp_reduce_body(a);
     sb_dp_signal(a.sync, 1);
 }
-__global__ void __launch_bounds__(256) sb_dp_post_kernel(SbDpPostArgs a) {
+__global__ void __launch_bounds__(256, 4) sb_dp_post_kernel(SbDpPostArgs a) {
     sb_dp_wait(a.sync, 1);
     sb_dp_post_body(a);
 }
@@ -389,17 +407,16 @@ int sb200_dp_stage(void* handle, int P, const float* d_means3D, const float* d_c
     return 0;
 }
 
-int sb200_dp_reduce(void* handle, int P, const int64_t* kf_ids, const float* global_scores, void* stream) {
+int sb200_dp_reduce(void* handle, int P, const float* global_scores, void* stream) {
     SbDpHandle* h = (SbDpHandle*)handle;
     if (!h || P < 0 || P > h->capacity) { sb_set_error("dp_reduce: bad handle / P"); return 1; }
-    if (!kf_ids || (P > 0 && !global_scores)) { sb_set_error("dp_reduce: NULL input"); return 1; }
+    if (P > 0 && !global_scores) { sb_set_error("dp_reduce: NULL input"); return 1; }
     const int S = sb200_dp_slice(h, P);
     SbDpReduceArgs a;
     memset(&a, 0, sizeof(a));
     for (int q = 0; q < h->n_ranks; q++) {
         a.peer_stage[q] = (const float*)(h->base[q] + h->L.stage);
         a.peer_vis[q] = (const uint8_t*)(h->base[q] + h->L.vis);
-        a.kf_ids[q] = kf_ids[q];
     }
     a.global_scores = global_scores;
     a.out = (float*)(h->base[h->rank] + h->L.out);
@@ -417,12 +434,12 @@ int sb200_dp_reduce(void* handle, int P, const int64_t* kf_ids, const float* glo
     return 0;
 }
 
-int sb200_dp_post(void* handle, int P, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
+int sb200_dp_post(void* handle, int P, const int64_t* kf_ids, float* const* params, float* const* exp_avg, float* const* exp_avg_sq,
                   const uint8_t* stable_mask, float* local_scores, float* global_scores, float* kf_max_scores,
                   int64_t* kf_id, const float* lr, float b1, float b2, float eps, void* stream) {
     SbDpHandle* h = (SbDpHandle*)handle;
     if (!h || P < 0 || P > h->capacity) { sb_set_error("dp_post: bad handle / P"); return 1; }
-    if (!params || !exp_avg || !exp_avg_sq || !lr || (P > 0 && (!stable_mask || !local_scores || !global_scores ||
+    if (!kf_ids || !params || !exp_avg || !exp_avg_sq || !lr || (P > 0 && (!stable_mask || !local_scores || !global_scores ||
                                                                  !kf_max_scores || !kf_id))) {
         sb_set_error("dp_post: NULL input");
         return 1;
@@ -437,6 +454,7 @@ int sb200_dp_post(void* handle, int P, float* const* params, float* const* exp_a
     for (int q = 0; q < h->n_ranks; q++) {
         a.peer_out[q] = (const float*)(h->base[q] + h->L.out);
         a.peer_upd[q] = (const uint8_t*)(h->base[q] + h->L.upd);
+        a.kf_ids[q] = kf_ids[q];
     }
     for (int g = 0; g < 5; g++) { a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g]; }
     a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;

@@ -120,9 +120,9 @@ def _load():
     lib.sb200_dp_stage.restype = _i32
     lib.sb200_dp_stage.argtypes = [_vp, _i32] + [_vp] * 11
     lib.sb200_dp_reduce.restype = _i32
-    lib.sb200_dp_reduce.argtypes = [_vp, _i32, _vp, _vp, _vp]
+    lib.sb200_dp_reduce.argtypes = [_vp, _i32, _vp, _vp]
     lib.sb200_dp_post.restype = _i32
-    lib.sb200_dp_post.argtypes = [_vp, _i32] + [_vp] * 9 + [_f32] * 3 + [_vp]
+    lib.sb200_dp_post.argtypes = [_vp, _i32] + [_vp] * 10 + [_f32] * 3 + [_vp]
     lib.sb200_knn_mean_dist2.restype = _i32
     lib.sb200_knn_mean_dist2.argtypes = [_i32, _vp, _vp, _vp]
     lib.sb200_prune_scratch_bytes.restype = _sz

@@ -323,8 +323,8 @@ class PeerExchange:
                                       _ptr(ws.d_rot), _ptr(ws.scores), _ptr(ws.radii), _ptr(params[2]), _ptr(params[3]),
                                       _ptr(params[4]), st), "sb200_dp_stage")
         kf_arr = (ctypes.c_int64 * self.world)(*[int(k) for k in kf_ids])
-        _check(lib.sb200_dp_reduce(h, P, kf_arr, _ptr(global_scores), st), "sb200_dp_reduce")
+        _check(lib.sb200_dp_reduce(h, P, _ptr(global_scores), st), "sb200_dp_reduce")
         lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
-        _check(lib.sb200_dp_post(h, P, _ptr_array(params), _ptr_array(exp_avg), _ptr_array(exp_avg_sq),
+        _check(lib.sb200_dp_post(h, P, kf_arr, _ptr_array(params), _ptr_array(exp_avg), _ptr_array(exp_avg_sq),
                                  _ptr(stable_mask), _ptr(local_scores), _ptr(global_scores), _ptr(kf_max_scores),
                                  _ptr(kf_id), lr_arr, float(betas[0]), float(betas[1]), float(eps), st), "sb200_dp_post")
