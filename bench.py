@@ -428,6 +428,19 @@ def run(emit):
             w = dpx.wait_ms()
             n_views = VIEWS_PER_STEP * (args.steps + args.warmup)
             dp_wait = {"before_reduce": w[0] / n_views, "before_post": w[1] / n_views}
+            # every rank's own numbers: its compute per view (all stages but the exchange's reduce / post), and how long
+            # its reduce / post kernels waited for the slowest peer -- tells view / GPU skew from exchange work
+            own = sum(ms / cnt for n, (ms, cnt) in stage_ms.items() if cnt and n not in ("dp_reduce", "dp_post"))
+            mine_row = torch.tensor([own, dp_wait["before_reduce"], dp_wait["before_post"],
+                                     stage_ms["blend_fwd"][0] / max(stage_ms["blend_fwd"][1], 1),
+                                     stage_ms["blend_bwd"][0] / max(stage_ms["blend_bwd"][1], 1)], device=dev, dtype=torch.float64)
+            rows = [torch.empty_like(mine_row) for _ in range(world)]
+            torch.distributed.all_gather(rows, mine_row)
+            dp_wait["by_rank"] = {"compute_ms_per_view": [round(float(r[0]), 4) for r in rows],
+                                  "wait_before_reduce": [round(float(r[1]), 4) for r in rows],
+                                  "wait_before_post": [round(float(r[2]), 4) for r in rows],
+                                  "blend_fwd_ms": [round(float(r[3]), 4) for r in rows],
+                                  "blend_bwd_ms": [round(float(r[4]), 4) for r in rows]}
         mapper.train_view = orig_train
     R_timed = R_seen
     ms_e2e, _, t2 = timed(step_e2e, args.steps, args.warmup)

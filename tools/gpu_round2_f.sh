@@ -7,7 +7,7 @@ N=${1:-8}
 RUN="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 timeout 300 $RUN --master-port 29521 tools/dp_check.py > $O/r02f_dp_check_${N}gpu.json 2> $O/r02f_dp_check_${N}gpu.err; echo "dp_check rc=$?"; tail -1 $O/r02f_dp_check_${N}gpu.json
 timeout 600 $RUN --master-port 29522 bench.py --gpus $N --steps 5 --warmup 3 > $O/r02f_bench_b200_C2_${N}gpu.json 2> $O/r02f_bench_b200_C2_${N}gpu.err; echo "bench p2p rc=$?"; tail -3 $O/r02f_bench_b200_C2_${N}gpu.err
-SB200_DP_EXCHANGE=nccl timeout 600 $RUN --master-port 29523 bench.py --gpus $N --steps 5 --warmup 3 --no-extras > $O/r02f_bench_b200_C2_${N}gpu_nccl.json 2> $O/r02f_bench_b200_C2_${N}gpu_nccl.err; echo "bench nccl rc=$?"
+[ -n "$SKIP_NCCL" ] || SB200_DP_EXCHANGE=nccl timeout 600 $RUN --master-port 29523 bench.py --gpus $N --steps 5 --warmup 3 --no-extras > $O/r02f_bench_b200_C2_${N}gpu_nccl.json 2> $O/r02f_bench_b200_C2_${N}gpu_nccl.err; echo "bench nccl rc=$?"
 python - <<'PY'
 import json, glob
 for f in sorted(glob.glob('gpurun_out/r02f_bench_*.json')):
