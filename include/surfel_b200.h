@@ -229,7 +229,8 @@ int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float
  * One optimizer step takes ONE view per rank (window views partitioned over the GPUs of a box, surfels replicated).
  * The calls below replace "sb200_surfel_update(DP_PRE) -> NCCL all-reduce of [16,P] -> sb200_surfel_update(DP_POST)" by
  * three kernels that read their peers' buffers directly and hand over to each other through flags in those buffers
- * (system-scope release / acquire; no barrier kernel, no collective call).  Surfel i is owned by rank i / slice.
+ * (system-scope release / acquire; no barrier kernel, no collective call).  Ownership is cyclic over 256-surfel
+ * chunks: surfel i is owned by rank (i / 256) % n_ranks.
  *   sb200_dp_create : rank's handle.  peer_bases: HOST array of n_ranks (<= 16) DEVICE pointers, entry q = rank q's
  *                     exchange buffer of sb200_dp_buffer_bytes(capacity, n_ranks) bytes, zero-filled, mapped into this
  *                     process (e.g. one torch symmetric-memory allocation per rank); every rank calls the three step

@@ -103,8 +103,8 @@ struct SbDpReduceArgs {
     const uint8_t* peer_vis[SB_DP_MAX_RANKS];
     const float* global_scores;   // [P,2] local replica (identical on every rank)
     float* out;                   // [slice, SB_DP_OUT_F] this rank's result rows
-    uint8_t* upd;                 // [slice] 1 = some view saw the surfel
-    int lo, hi, n_ranks;
+    uint8_t* upd;                 // [slice] 0 = no view saw the surfel, else 1 + rank of the first arg-max of score 0
+    int P, rank, n_ranks;         // ownership is cyclic over 256-surfel chunks: chunk c belongs to rank c % n_ranks
     SbDpSync sync;
 };
 
@@ -115,11 +115,13 @@ struct SbDpReduceArgs {
 __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
     __shared__ float4 s_rows[2][256 * (SB_DP_STAGE_F / 4)];   // double buffered: the next rank's span arrives while this one is folded
     __shared__ uint32_t s_any;                                // bit q: rank q's view saw one of this CTA's surfels
-    const int i0 = a.lo + blockIdx.x * blockDim.x;       // first surfel of this CTA (lo and the slice are multiples of 256)
+    // CTA b of rank r folds chunk b * n_ranks + r (cyclic ownership: the surfels a window sees are clustered in index,
+    // contiguous slices left the owners of the old end of the cloud idle and the others with 3x the average work)
+    const int i0 = (blockIdx.x * a.n_ranks + a.rank) * 256;
     const int i = i0 + threadIdx.x;
-    const bool mine = i < a.hi;
-    const size_t iz = (size_t)(mine ? i : a.lo);
-    const int rows = min(256, a.hi - i0);                // rows of this CTA inside the slice
+    const bool mine = i < a.P;
+    const size_t iz = (size_t)(mine ? i : 0);
+    const int rows = max(0, min(256, a.P - i0));         // rows of this chunk that exist
     // every rank's visibility byte first: n_ranks independent peer loads in flight, not a chain of them
     uint32_t vis_bits = 0;
     if (threadIdx.x == 0) s_any = 0;
@@ -166,7 +168,7 @@ __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
         buf ^= 1;
     }
     if (!mine) return;
-    const int li = i - a.lo;
+    const int li = blockIdx.x * 256 + threadIdx.x;       // the chunk's place in the owner's result buffer
     a.upd[li] = vis_bits ? (uint8_t)(1 + arg_rank) : 0;
     if (!vis_bits) return;
     float4* o = (float4*)(a.out + (size_t)li * SB_DP_OUT_F);
@@ -185,7 +187,7 @@ struct SbDpPostArgs {
     float lr[5];
     float b1, b2, eps;
     long long kf_ids[SB_DP_MAX_RANKS];   // keyframe id of every rank's view of this step
-    int P, slice;
+    int P, n_ranks;
     SbDpSync sync;
 };
 
@@ -195,11 +197,11 @@ struct SbDpPostArgs {
 
 __device__ __forceinline__ void sb_dp_post_body(const SbDpPostArgs& a) {
     __shared__ float4 s_rows[256 * (SB_DP_OUT_F / 4)];
-    const int i0 = blockIdx.x * blockDim.x;              // 256 consecutive surfels: one owner (the slice is a multiple of 256)
+    const int i0 = blockIdx.x * blockDim.x;              // one 256-surfel chunk: one owner
     const int i = i0 + threadIdx.x;
     const bool inside = i < a.P;
     const size_t iz = (size_t)(inside ? i : 0);
-    const int owner = i0 / a.slice, l0 = i0 - owner * a.slice;
+    const int chunk = blockIdx.x, owner = chunk % a.n_ranks, l0 = (chunk / a.n_ranks) * 256;
     // The owner's touched byte and its span of result rows are requested together (one peer round trip, not two); the
     // span of a CTA nobody touched is fetched for nothing, which costs NVLink bytes but no latency.
     const uint32_t ub = inside ? sb_ld_peer_u8(a.peer_upd[owner] + l0 + threadIdx.x) : 0u;
@@ -289,7 +291,7 @@ struct SbDpLayout { size_t stage, vis, out, upd, flags, counter, error, wait, to
 static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
     SbDpLayout L;
     const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
-    L.slice_cap = (int64_t)((((cap + n_ranks - 1) / n_ranks) + 255) / 256 * 256);
+    L.slice_cap = (int64_t)(((cap + 255) / 256 + n_ranks - 1) / n_ranks * 256);   // chunks per owner, rounded up
     size_t o = 0;
     L.stage = o;   o = sb_align(o + cap * SB_DP_STAGE_F * 4);
     L.vis = o;     o = sb_align(o + cap);
@@ -360,9 +362,11 @@ void* sb200_dp_create(int rank, int n_ranks, int64_t capacity, const void* const
 
 void sb200_dp_destroy(void* handle) { delete (SbDpHandle*)handle; }
 
-int sb200_dp_slice(void* handle, int P) {
+int sb200_dp_slice(void* handle, int P) {   // rows of the result buffer a rank needs for P surfels
     SbDpHandle* h = (SbDpHandle*)handle;
-    return h ? (int)((((P + h->n_ranks - 1) / h->n_ranks) + 255) / 256 * 256) : 0;
+    if (!h) return 0;
+    const int chunks = (P + 255) / 256;
+    return (chunks + h->n_ranks - 1) / h->n_ranks * 256;
 }
 
 int sb200_dp_error(void* handle, void* stream) {
@@ -411,7 +415,6 @@ int sb200_dp_reduce(void* handle, int P, const float* global_scores, void* strea
     SbDpHandle* h = (SbDpHandle*)handle;
     if (!h || P < 0 || P > h->capacity) { sb_set_error("dp_reduce: bad handle / P"); return 1; }
     if (P > 0 && !global_scores) { sb_set_error("dp_reduce: NULL input"); return 1; }
-    const int S = sb200_dp_slice(h, P);
     SbDpReduceArgs a;
     memset(&a, 0, sizeof(a));
     for (int q = 0; q < h->n_ranks; q++) {
@@ -421,14 +424,13 @@ int sb200_dp_reduce(void* handle, int P, const float* global_scores, void* strea
     a.global_scores = global_scores;
     a.out = (float*)(h->base[h->rank] + h->L.out);
     a.upd = (uint8_t*)(h->base[h->rank] + h->L.upd);
-    a.lo = P < h->rank * S ? P : h->rank * S;
-    a.hi = P < (h->rank + 1) * S ? P : (h->rank + 1) * S;
-    a.n_ranks = h->n_ranks;
+    a.P = P; a.rank = h->rank; a.n_ranks = h->n_ranks;
     a.sync = sb_dp_sync_of(h);
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_DP_REDUCE, s);
-    const int n = a.hi - a.lo;
-    sb_dp_reduce_kernel<<<(n + 255) / 256 + (n == 0), 256, 0, s>>>(a);
+    const int chunks = (P + 255) / 256;
+    const int mine = chunks > h->rank ? (chunks - h->rank + h->n_ranks - 1) / h->n_ranks : 0;   // chunks r, r + N, ...
+    sb_dp_reduce_kernel<<<mine > 0 ? mine : 1, 256, 0, s>>>(a);   // at least one CTA: it carries the hand-off
     sb_count_launch(1);
     SB_CUDA_CHECK(cudaGetLastError());
     return 0;
@@ -458,8 +460,7 @@ int sb200_dp_post(void* handle, int P, const int64_t* kf_ids, float* const* para
     }
     for (int g = 0; g < 5; g++) { a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g]; }
     a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;
-    a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.slice = sb200_dp_slice(h, P);
-    if (a.slice < 1) a.slice = 256;
+    a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.n_ranks = h->n_ranks;
     a.sync = sb_dp_sync_of(h);
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_DP_POST, s);
