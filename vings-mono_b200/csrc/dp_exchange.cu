@@ -104,6 +104,7 @@ struct SbDpReduceArgs {
     const float* global_scores;   // [P,2] local replica (identical on every rank)
     float* out;                   // [slice, SB_DP_OUT_F] this rank's result rows
     uint8_t* upd;                 // [slice] 0 = no view saw the surfel, else 1 + rank of the first arg-max of score 0
+    uint8_t* peer_chunk[SB_DP_MAX_RANKS];   // every rank's chunk-touched bytes: the owner PUSHES its verdict to all of them
     int P, rank, n_ranks;         // ownership is cyclic over 256-surfel chunks: chunk c belongs to rank c % n_ranks
     SbDpSync sync;
 };
@@ -135,6 +136,9 @@ __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
     const float glob0 = mine ? a.global_scores[2 * iz] : 0.0f;
     __syncthreads();
     uint32_t todo = s_any;
+    // tell every rank whether anything in this chunk was seen: their post kernels then fetch the result span only if
+    // so, without a peer round trip for the answer (remote stores, released by this kernel's hand-off signal)
+    if ((int)threadIdx.x < a.n_ranks && rows > 0) a.peer_chunk[threadIdx.x][i0 >> 8] = todo ? 1 : 0;
     float acc[13];
 #pragma unroll
     for (int c = 0; c < 13; c++) acc[c] = 0.0f;
@@ -187,6 +191,7 @@ struct SbDpPostArgs {
     float lr[5];
     float b1, b2, eps;
     long long kf_ids[SB_DP_MAX_RANKS];   // keyframe id of every rank's view of this step
+    const uint8_t* chunk;                // local chunk-touched bytes (written by the owners' reduce kernels)
     int P, n_ranks;
     SbDpSync sync;
 };
@@ -202,8 +207,9 @@ __device__ __forceinline__ void sb_dp_post_body(const SbDpPostArgs& a) {
     const bool inside = i < a.P;
     const size_t iz = (size_t)(inside ? i : 0);
     const int chunk = blockIdx.x, owner = chunk % a.n_ranks, l0 = (chunk / a.n_ranks) * 256;
-    // The owner's touched byte and its span of result rows are requested together (one peer round trip, not two); the
-    // span of a CTA nobody touched is fetched for nothing, which costs NVLink bytes but no latency.
+    // nobody saw any surfel of this chunk (the owner said so, into local memory): nothing to fetch, nothing to do
+    if (a.chunk[chunk] == 0) return;
+    // the owner's touched bytes and its span of result rows are requested together (one peer round trip, not two)
     const uint32_t ub = inside ? sb_ld_peer_u8(a.peer_upd[owner] + l0 + threadIdx.x) : 0u;
     {
         const int rows = min(256, a.P - i0);
@@ -287,7 +293,7 @@ __global__ void __launch_bounds__(256, 4) sb_dp_post_kernel(SbDpPostArgs a) {
 }
 
 // ---- host side: one exchange handle per rank (layout of the peer-mapped buffer, peer pointers, step counter) ----
-struct SbDpLayout { size_t stage, vis, out, upd, flags, counter, error, wait, total; int64_t slice_cap; };
+struct SbDpLayout { size_t stage, vis, out, upd, chunk, flags, counter, error, wait, total; int64_t slice_cap; };
 static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
     SbDpLayout L;
     const size_t cap = (size_t)(capacity > 0 ? capacity : 0);
@@ -297,6 +303,7 @@ static SbDpLayout sb_dp_layout(int64_t capacity, int n_ranks) {
     L.vis = o;     o = sb_align(o + cap);
     L.out = o;     o = sb_align(o + (size_t)L.slice_cap * SB_DP_OUT_F * 4);
     L.upd = o;     o = sb_align(o + (size_t)L.slice_cap);
+    L.chunk = o;   o = sb_align(o + (cap + 255) / 256);   // one byte per 256-surfel chunk: some view saw one of its surfels
     L.flags = o;   o = sb_align(o + 2 * SB_DP_MAX_RANKS * 4);
     L.counter = o; o = sb_align(o + 2 * 4);
     L.error = o;   o = sb_align(o + 4);
@@ -420,6 +427,7 @@ int sb200_dp_reduce(void* handle, int P, const float* global_scores, void* strea
     for (int q = 0; q < h->n_ranks; q++) {
         a.peer_stage[q] = (const float*)(h->base[q] + h->L.stage);
         a.peer_vis[q] = (const uint8_t*)(h->base[q] + h->L.vis);
+        a.peer_chunk[q] = (uint8_t*)(h->base[q] + h->L.chunk);
     }
     a.global_scores = global_scores;
     a.out = (float*)(h->base[h->rank] + h->L.out);
@@ -461,6 +469,7 @@ int sb200_dp_post(void* handle, int P, const int64_t* kf_ids, float* const* para
     for (int g = 0; g < 5; g++) { a.param[g] = params[g]; a.m[g] = exp_avg[g]; a.v[g] = exp_avg_sq[g]; a.lr[g] = lr[g]; }
     a.stable = stable_mask; a.local_scores = local_scores; a.global_scores = global_scores; a.kf_max = kf_max_scores;
     a.kf_id = (long long*)kf_id; a.b1 = b1; a.b2 = b2; a.eps = eps; a.P = P; a.n_ranks = h->n_ranks;
+    a.chunk = (const uint8_t*)(h->base[h->rank] + h->L.chunk);
     a.sync = sb_dp_sync_of(h);
     cudaStream_t s = (cudaStream_t)stream;
     SbStageScope sc(SB200_STAGE_DP_POST, s);
