@@ -213,7 +213,11 @@ int sb200_surfel_update(int P, int mode, float* const* params, float* const* exp
  *   mode 0: single-GPU update (SB200_UPDATE_LOCAL semantics).
  *   mode 1: multi-GPU stage - does what sb200_dp_stage does (stage rows of visible surfels, visibility bytes, signal to
  *           the peers) on the exchange handle `dp` and updates nothing; exp_avg .. lr may be NULL.
- *   R < 0 (test hook): skip the blend, grad_ws already holds the view's accumulation records. */
+ *   mode | SB200_BWD_RECORDS_ZERO: grad_ws is known to be all zero on entry, skip its memset.  The call always hands
+ *           grad_ws back all zero (the per-surfel pass zeroes the records it consumed; only visible surfels ever
+ *           receive any), so a caller that uses nothing else on that buffer sets the bit on every call but the first.
+ *   R < 0 (test hook): skip the blend, grad_ws already holds the view's accumulation records (left untouched). */
+#define SB200_BWD_RECORDS_ZERO 4
 int sb200_backward_update(int P, int W, int H, int64_t R, const float* bg, float tanfovx, float tanfovy,
                           const float* means3D, const float* scales, const float* rotations,
                           const float* viewmatrix, const float* projmatrix, const int* radii,

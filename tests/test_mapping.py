@@ -403,6 +403,11 @@ def test_backward_update_equals_backward_then_update():
     vds = [mapper_step.view_to_device(v, dev) for v in views[:2]]
     m.train_view(vds[1], gts[1], kf_id=4)   # non-trivial moments and scores (through backward_update itself)
     assert float(m.optimizer.state[m._xyz]["exp_avg"].abs().sum()) > 0
+    # the call hands the accumulation records back zeroed (only consumed ones are rewritten), so the next one needs
+    # no memset: SB200_BWD_RECORDS_ZERO
+    assert m._ws.grad_zero and not bool(m._ws.grad_ws.any())
+    m.train_view(vds[0], gts[0], kf_id=5)   # ... and this view ran without the memset
+    assert m._ws.grad_zero and not bool(m._ws.grad_ws.any())
     P, ws = m.P, m._ws
     prm = [getattr(m, k).data for k in mapper_step.GROUPS]
     lr = [mapper_step.LR[k] for k in mapper_step.GROUPS]

@@ -239,7 +239,8 @@ struct SbViewUpdateArgs {
     SbUpdateArgs u;                // params, moments, bookkeeping, lr, betas (gradient pointers unused)
     const float* means3D; const float* act_scales; const float* act_rot;   // the rasterizer's inputs of this view
     const float* viewmatrix; const float* projmatrix;
-    const float* grad_acc;         // [P, SB_GRAD_F] the backward blend's accumulation records
+    float* grad_acc;               // [P, SB_GRAD_F] the backward blend's accumulation records
+    int rezero;                    // hand every consumed record back zeroed (the next backward then needs no memset)
     float* stage; uint8_t* vis;    // MODE 1
     SbDpSync sync;                 // MODE 1: hand-off to the peers' reduce kernels
     int Wq, Hq;
@@ -257,11 +258,17 @@ __device__ __forceinline__ void sb_view_update_body(const SbViewUpdateArgs& va, 
 
     float acc[SB_GRAD_F];
     {
-        const float4* ga = reinterpret_cast<const float4*>(va.grad_acc + iz * SB_GRAD_F);
+        float4* ga = reinterpret_cast<float4*>(va.grad_acc + iz * SB_GRAD_F);
 #pragma unroll
         for (int k = 0; k < SB_GRAD_F / 4; k++) {
             const float4 v = ga[k];
             acc[4 * k] = v.x; acc[4 * k + 1] = v.y; acc[4 * k + 2] = v.z; acc[4 * k + 3] = v.w;
+        }
+        // only visible surfels ever receive REDs, so zeroing what was consumed keeps the whole buffer zero: 80 B x V
+        // written here instead of an 80 B x P memset in front of every backward blend
+        if (va.rezero) {
+#pragma unroll
+            for (int k = 0; k < SB_GRAD_F / 4; k++) ga[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
     }
     float3 d_mean3D = {0.f, 0.f, 0.f};
@@ -404,6 +411,8 @@ extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float
                                      const uint8_t* stable_mask, float* local_scores, float* global_scores,
                                      float* kf_max_scores, int64_t* kf_id, int64_t kf, const float* lr, float b1,
                                      float b2, float eps, void* dp, void* stream) {
+    const bool known_zero = (mode & SB200_BWD_RECORDS_ZERO) != 0;   // grad_ws is zero on entry (left so by the previous call)
+    mode &= ~SB200_BWD_RECORDS_ZERO;
     if (P < 0 || W <= 0 || H <= 0 || (mode != 0 && mode != 1)) { sb_set_error("backward_update: bad P / size / mode"); return 1; }
     if (P == 0 && mode == 1) { sb_set_error("backward_update: the multi-GPU exchange needs at least one surfel"); return 1; }
     if (P == 0) return 0;
@@ -420,7 +429,7 @@ extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float
     int rc;
     if (R >= 0) {   // R < 0 (test hook): grad_ws already holds this view's accumulation records
         SbStageScope sc(SB200_STAGE_BLEND_BWD, s);
-        SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
+        if (!known_zero) SB_CUDA_CHECK(cudaMemsetAsync(grad_ws, 0, (size_t)P * SB_GRAD_F * 4, s));
         if (R > 0) {
             rc = sb_launch_blend_backward(W, H, bg, (const char*)geom_ws, point_list, (const char*)image_ws, out_color,
                                           out_others, dL_dout_color, dL_dout_others, (const bool*)pixel_mask,
@@ -442,7 +451,8 @@ extern "C" int sb200_backward_update(int P, int W, int H, int64_t R, const float
     va.u.kf_max = kf_max_scores; va.u.kf_id = (long long*)kf_id; va.u.b1 = b1; va.u.b2 = b2; va.u.eps = eps; va.u.kf = kf;
     va.u.P = P; va.u.mode = mode;
     va.means3D = means3D; va.act_scales = scales; va.act_rot = rotations; va.viewmatrix = viewmatrix; va.projmatrix = projmatrix;
-    va.grad_acc = (const float*)grad_ws;
+    va.grad_acc = (float*)grad_ws;
+    va.rezero = R >= 0;   // (the R < 0 test hook reads records somebody else still needs)
     if (mode == 1 && sb_dp_begin_step(dp, P, &va.stage, &va.vis, &va.sync)) return 1;
     SbStageScope sc(SB200_STAGE_UPDATE, s);
     return sb_launch_view_update(mode, W, H, tanfovx, tanfovy, va, s);

@@ -109,6 +109,7 @@ class RasterWorkspace:
         self.capacity = cap
         self.geom = torch.empty(lib.sb200_geom_bytes(cap), dtype=torch.uint8, device=dev)
         self.grad_ws = torch.empty(lib.sb200_grad_bytes(cap), dtype=torch.uint8, device=dev)
+        self.grad_zero = False   # True while grad_ws is known to be all zero (backward_update leaves it so)
         self._rows = dict(radii=torch.empty(cap, dtype=torch.int32, device=dev), d_means3D=f(cap, 3), d_means2D=f(cap, 3),
                           d_colors=f(cap, 3), d_opacity=f(cap, 1), d_scales=f(cap, 2), d_rot=f(cap, 4), scores=f(cap, 2),
                           act_opacity=f(cap, 1), act_scales=f(cap, 2), act_rot=f(cap, 4))
@@ -199,6 +200,7 @@ class RasterWorkspace:
                  pixel_mask=None):
         lib = _load()
         mask = self.pixel_mask if pixel_mask is None else pixel_mask
+        self.grad_zero = False   # sb200_backward leaves the accumulation records in place
         _check(lib.sb200_backward(self.P, self.W, self.H, self.R, _ptr(bg), float(tanfovx), float(tanfovy),
                                   _ptr(means3D), _ptr(scales), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix),
                                   _ptr(self.radii), _ptr(self.geom), _vp(self.point_list.data_ptr()), _ptr(self.image),
@@ -218,6 +220,11 @@ def backward_update(ws, mode, d_color, d_allmap, means3D, scales, rotations, bg,
     mask = ws.pixel_mask if pixel_mask is None else pixel_mask
     lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
     null = _vp(None)
+    if not reuse_records:
+        # the call leaves grad_ws all zero; if nothing else has written it since, the next call skips the memset
+        if ws.grad_zero:
+            mode = int(mode) | 4   # SB200_BWD_RECORDS_ZERO
+        ws.grad_zero = True
     _check(lib.sb200_backward_update(
         ws.P, ws.W, ws.H, -1 if reuse_records else ws.R, _ptr(bg), float(tanfovx), float(tanfovy), _ptr(means3D),
         _ptr(scales), _ptr(rotations), _ptr(viewmatrix), _ptr(projmatrix), _ptr(ws.radii), _ptr(ws.geom),
