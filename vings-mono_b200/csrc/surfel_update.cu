@@ -264,12 +264,7 @@ __device__ __forceinline__ void sb_view_update_body(const SbViewUpdateArgs& va, 
             const float4 v = ga[k];
             acc[4 * k] = v.x; acc[4 * k + 1] = v.y; acc[4 * k + 2] = v.z; acc[4 * k + 3] = v.w;
         }
-        // only visible surfels ever receive REDs, so zeroing what was consumed keeps the whole buffer zero: 80 B x V
-        // written here instead of an 80 B x P memset in front of every backward blend
-        if (va.rezero) {
-#pragma unroll
-            for (int k = 0; k < SB_GRAD_F / 4; k++) ga[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
+
     }
     float3 d_mean3D = {0.f, 0.f, 0.f};
     float2 d_scale = {0.f, 0.f};
@@ -312,6 +307,15 @@ __device__ __forceinline__ void sb_view_update_body(const SbViewUpdateArgs& va, 
         kfm = a.kf_max[i];
     }
 
+    // Only visible surfels ever receive REDs, so zeroing what was consumed keeps the whole buffer zero: 80 B x V written
+    // here instead of an 80 B x P memset in front of every backward blend.  Placed behind the last load of the pass:
+    // a store in front of the parameter / moment loads serialises them (the compiler must assume aliasing) and doubled
+    // this kernel's time.
+    if (va.rezero) {
+        float4* ga = reinterpret_cast<float4*>(va.grad_acc + iz * SB_GRAD_F);
+#pragma unroll
+        for (int k = 0; k < SB_GRAD_F / 4; k++) ga[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     // ---- backward of the activations: the expressions of sb_surfel_update_kernel / sb_dp_stage_kernel ----
     {
         const float y = 1.0f / (1.0f + expf(-pv[6]));

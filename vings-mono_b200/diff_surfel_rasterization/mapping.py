@@ -108,8 +108,8 @@ class RasterWorkspace:
         f = lambda *s: torch.empty(s, dtype=torch.float32, device=dev)
         self.capacity = cap
         self.geom = torch.empty(lib.sb200_geom_bytes(cap), dtype=torch.uint8, device=dev)
-        self.grad_ws = torch.empty(lib.sb200_grad_bytes(cap), dtype=torch.uint8, device=dev)
-        self.grad_zero = False   # True while grad_ws is known to be all zero (backward_update leaves it so)
+        self.grad_ws = torch.zeros(lib.sb200_grad_bytes(cap), dtype=torch.uint8, device=dev)
+        self.grad_zero = True    # True while ALL of grad_ws is known to be zero (backward_update leaves it so)
         self._rows = dict(radii=torch.empty(cap, dtype=torch.int32, device=dev), d_means3D=f(cap, 3), d_means2D=f(cap, 3),
                           d_colors=f(cap, 3), d_opacity=f(cap, 1), d_scales=f(cap, 2), d_rot=f(cap, 4), scores=f(cap, 2),
                           act_opacity=f(cap, 1), act_scales=f(cap, 2), act_rot=f(cap, 4))
@@ -221,9 +221,12 @@ def backward_update(ws, mode, d_color, d_allmap, means3D, scales, rotations, bg,
     lr_arr = (ctypes.c_float * 5)(*[float(x) for x in lr])
     null = _vp(None)
     if not reuse_records:
-        # the call leaves grad_ws all zero; if nothing else has written it since, the next call skips the memset
-        if ws.grad_zero:
-            mode = int(mode) | 4   # SB200_BWD_RECORDS_ZERO
+        # the call hands grad_ws back all zero, so the next one needs no memset (SB200_BWD_RECORDS_ZERO); after anything
+        # else wrote records (sb200_backward leaves them in place) the WHOLE capacity is cleared once: rows beyond the
+        # current P come into use when the map grows
+        if not ws.grad_zero:
+            ws.grad_ws.zero_()
+        mode = int(mode) | 4
         ws.grad_zero = True
     _check(lib.sb200_backward_update(
         ws.P, ws.W, ws.H, -1 if reuse_records else ws.R, _ptr(bg), float(tanfovx), float(tanfovy), _ptr(means3D),
