@@ -289,6 +289,24 @@ size_t sb200_prune_scratch_bytes(int64_t P);
 int sb200_prune_rows(int P, const uint8_t* delete_mask, int n_arrays, const void* const* src, void* const* dst,
                      const int* row_bytes, void* scratch, int* kept_host, void* stream);
 
+/* sb200_prune_rows_static: sb200_prune_rows for callers that cannot allocate (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  It has NO counterpart in the reference.
+ * Same compaction, same kernels, same dst contents; the differences:
+ *   - no scratch argument: the block counts live in a file-scope `static __device__` array of the library
+ *     (SB200_PRUNE_STATIC_MAX_ROWS / 1024 + 2 words = 64 KiB + 8 B, held by every GPU that loads the library until
+ *     exit).  P > SB200_PRUNE_STATIC_MAX_ROWS is rejected with return 1 and a message in sb200_last_error();
+ *   - kept_dev is a DEVICE pointer to one int32 that receives the surviving row count in stream order; there is
+ *     no host read-back and no synchronisation (P == 0 stores 0);
+ *   - the call makes no cudaMalloc / cudaFree / allocating library call: three launches and one 4-byte
+ *     device-to-device copy on `stream` (the first call on each device also resolves the array's address with
+ *     cudaGetSymbolAddress); it is not bracketed by the optional stage profiling, whose events are allocations.
+ * Every call on a device shares the one array, which keeps the previous call's contents; nothing in it has to start
+ * at zero (each call rewrites every word it reads before reading it).  Calls that overlap on the same GPU (two
+ * streams, two threads) RACE on it: serialise them, or use sb200_prune_rows with one scratch buffer per stream. */
+#define SB200_PRUNE_STATIC_MAX_ROWS (16 * 1024 * 1024)
+int sb200_prune_rows_static(int P, const uint8_t* delete_mask, int n_arrays, const void* const* src, void* const* dst,
+                            const int* row_bytes, int* kept_dev, void* stream);
+
 /* ---- precomputed splat transforms (the rasterizer's `cov3D_precomp` = transMat_precomp input; unused by VINGS-Mono) ----
  * transMat_precomp [P,9]: rows Tu, Tv, Tw of every surfel's splat-to-pixel transform, used instead of scales +
  * rotations (cuda_rasterizer/forward.cu:204-219: the normal becomes (0,0,1)).  Stage 2 is sb200_forward_finish.

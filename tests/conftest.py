@@ -17,12 +17,12 @@ def pytest_configure(config):
 # driver's `pytest -x` a failure in a caller-side test can never hide the hot-path parity suite again (round 1).
 _ORDER = ("test_oracle_golden", "test_parity_gpu", "test_parity_full_gpu", "test_ops_gpu", "test_mapping",
           "test_sh_gpu", "test_host_cpu", "test_block_cull_cpu", "test_formats", "test_mapper_gloo", "test_multigpu",
-          "test_churn")
+          "test_churn", "test_zz_no_alloc")   # test_zz_no_alloc stays last: nothing can hide behind a failure in it
 
 
 def _rank(item):
     name = os.path.splitext(os.path.basename(str(item.fspath)))[0]
-    return _ORDER.index(name) if name in _ORDER else len(_ORDER) - 1
+    return _ORDER.index(name) if name in _ORDER else len(_ORDER) - 2
 
 
 def pytest_collection_modifyitems(config, items):

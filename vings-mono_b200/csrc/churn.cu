@@ -13,6 +13,7 @@
 //                            in three launches (block counts, scan of the counts, fused gather of all arrays) from one
 //                            capacity buffer set into the other; one 4-byte read-back of the surviving count.
 #include "common.cuh"
+#include <mutex>
 #include "../../include/surfel_b200.h"
 
 #define KNN_THREADS 256
@@ -215,3 +216,66 @@ int sb200_prune_rows(int P, const uint8_t* delete_mask, int n_arrays, const void
 }
 
 }  // extern "C"
+
+// ---- sb200_prune_rows_static: the same compaction for callers that must not allocate -------------------------------
+// No counterpart in the reference (include/surfel_b200.h).  The block
+// counts live in a file-scope device array instead of caller scratch: 64 KiB + 8 B of every GPU that loads the library,
+// held until exit.  Host code cannot use the symbol's name as a pointer (it is a host-side stand-in, not a device
+// address): the address is taken once per device with cudaGetSymbolAddress, with that device current.
+static __device__ __align__(256) uint32_t g_prune_static_counts[SB200_PRUNE_STATIC_MAX_ROWS / PR_ROWS + 2];
+
+static int sb_prune_static_scratch(uint32_t** out) {
+    static std::mutex mu;
+    static uint32_t* ptr_dev[SB_MAX_DEVICES] = {};
+    int dev = -1;
+    SB_CUDA_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= SB_MAX_DEVICES) { sb_set_error("prune_static: device %d out of range", dev); return 1; }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptr_dev[dev]) {
+        uint32_t* p = nullptr;
+        SB_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_prune_static_counts));
+        if (!p) { sb_set_error("prune_static: cudaGetSymbolAddress returned NULL"); return 2; }
+        ptr_dev[dev] = p;
+    }
+    *out = ptr_dev[dev];
+    return 0;
+}
+
+extern "C" int sb200_prune_rows_static(int P, const uint8_t* delete_mask, int n_arrays, const void* const* src,
+                                       void* const* dst, const int* row_bytes, int* kept_dev, void* stream) {
+    if (P < 0 || n_arrays < 0 || n_arrays > SB200_PRUNE_MAX_ARRAYS) { sb_set_error("prune_static: bad P / n_arrays"); return 1; }
+    if (P > SB200_PRUNE_STATIC_MAX_ROWS) {
+        sb_set_error("prune_static: P = %d exceeds SB200_PRUNE_STATIC_MAX_ROWS = %d (the static scratch is fixed; use "
+                     "sb200_prune_rows with caller scratch)", P, (int)SB200_PRUNE_STATIC_MAX_ROWS);
+        return 1;
+    }
+    if (!kept_dev) { sb_set_error("prune_static: kept_dev is NULL"); return 1; }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (P == 0) {
+        SB_CUDA_CHECK(cudaMemsetAsync(kept_dev, 0, 4, s));
+        return 0;
+    }
+    if (!delete_mask || (n_arrays > 0 && (!src || !dst || !row_bytes))) { sb_set_error("prune_static: NULL input"); return 1; }
+    SbPruneArrays A;
+    A.n = n_arrays;
+    for (int a = 0; a < n_arrays; a++) {
+        if (row_bytes[a] <= 0) { sb_set_error("prune_static: row_bytes[%d] must be positive", a); return 1; }
+        if (!src[a] || !dst[a] || src[a] == dst[a]) { sb_set_error("prune_static: array %d needs distinct src and dst buffers", a); return 1; }
+        if (row_bytes[a] % 4 == 0 && (((uintptr_t)src[a] | (uintptr_t)dst[a]) & 3)) { sb_set_error("prune_static: array %d is not 4-byte aligned", a); return 1; }
+        A.src[a] = (const uint8_t*)src[a];
+        A.dst[a] = (uint8_t*)dst[a];
+        A.bytes[a] = row_bytes[a];
+    }
+    uint32_t* counts = nullptr;
+    if (int rc = sb_prune_static_scratch(&counts)) return rc;
+    const int nblocks = (P + PR_ROWS - 1) / PR_ROWS;
+    // Nothing in the array has to start at zero: the count kernel writes counts[0 .. nblocks) and the scan writes
+    // counts[nblocks] before anything reads them, so the previous call's contents are dead.
+    sb_prune_count_kernel<<<nblocks, PR_THREADS, 0, s>>>(P, delete_mask, counts);
+    sb_prune_scan_kernel<<<1, 1024, 0, s>>>(nblocks, counts);
+    sb_prune_gather_kernel<<<nblocks, PR_THREADS, 0, s>>>(P, delete_mask, counts, A);
+    sb_count_launch(3);
+    SB_CUDA_CHECK(cudaGetLastError());
+    SB_CUDA_CHECK(cudaMemcpyAsync(kept_dev, counts + nblocks, 4, cudaMemcpyDeviceToDevice, s));
+    return 0;
+}

@@ -129,6 +129,8 @@ def _load():
     lib.sb200_prune_scratch_bytes.argtypes = [_i64]
     lib.sb200_prune_rows.restype = _i32
     lib.sb200_prune_rows.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp, _vp]
+    lib.sb200_prune_rows_static.restype = _i32   # no caller scratch, device-side count (include/surfel_b200.h)
+    lib.sb200_prune_rows_static.argtypes = [_i32, _vp, _i32, _vp, _vp, _vp, _vp, _vp]
     if lib.sb200_abi_version() != 7:
         raise RuntimeError("libsurfel_b200.so ABI mismatch")
     _lib = lib
