@@ -15,8 +15,8 @@
 //                        visibility into a byte array.  Local stores only.
 //   -- hand-off: the LAST CTA of the stage kernel release-stores the step number into every peer's flag block; every
 //      CTA of the next kernel spins (acquire, system scope) on its own rank's flags before it touches peer rows --
-//   sb_dp_reduce_kernel  (rank r, its slice of the surfels)   a reduce-scatter by peer LOADS: for the surfels it
-//                        owns the rank reads the stage rows of the ranks that saw them, applies weighting_grad per
+//   sb_dp_reduce_kernel  (rank r, the 256-surfel chunks c with c % N == r)   a reduce-scatter by peer LOADS: for the
+//                        surfels it owns the rank reads the stage rows of the ranks that saw them, applies weighting_grad per
 //                        view (scripts/gaussian/gaussian_utils.py:56-62) and folds the views IN RANK ORDER into one
 //                        64-B result row: gradient sum, add_records' running quantities (gaussian_model.py:163-168:
 //                        score sum, max of the second score, max of the first score; the rank of its first arg-max
@@ -33,7 +33,7 @@
 // reduce waits for every peer's next stage, which follows that peer's post (the readers of its result rows).
 //
 // Bytes over NVLink per rank and step at C2 on 8 GPUs: stage rows 7/8 * (P/8) * 8 * 0.41 * 64 B = 22 MB in, result
-// rows 7/8 * ~0.6 P * 80 B = 50 MB in, against 2 * 7/8 * 77 MB = 134 MB for the dense all-reduce.
+// rows 7/8 * ~0.6 P * 64 B = 40 MB in, against 2 * 7/8 * 77 MB = 134 MB for the dense all-reduce.
 #include "dp_sync.cuh"
 #include <string.h>
 #include "../../include/surfel_b200.h"
@@ -110,8 +110,8 @@ struct SbDpReduceArgs {
 };
 
 // Rows that live on another GPU are fetched the way NVLink likes them: the CTA's 256 consecutive rows are one
-// contiguous 16 KB (stage) / 20 KB (result) span, loaded with fully coalesced 512-byte warp requests into shared memory
-// and only then picked apart per thread.  (Per-thread row loads -- 16-byte pieces at a 64 / 80-byte stride -- ran the
+// contiguous 16 KB span (stage and result rows are both 64 B), loaded with fully coalesced 512-byte warp requests into shared memory
+// and only then picked apart per thread.  (Per-thread row loads -- 16-byte pieces at a 64-byte stride, 80 before the result row was packed -- ran the
 // 2-GPU post kernel at ~110 GB/s of NVLink reads: 0.26 ms for 29 MB.)
 __device__ __forceinline__ void sb_dp_reduce_body(const SbDpReduceArgs& a) {
     __shared__ float4 s_rows[2][256 * (SB_DP_STAGE_F / 4)];   // double buffered: the next rank's span arrives while this one is folded
