@@ -32,6 +32,7 @@
 //     in the reference, which evaluates all 256 pixels of a tile for every surfel.
 #include "pair_math.cuh"
 #include "ring.cuh"
+#include <mutex>
 
 #define BB_CWARPS 8
 #define BB_THREADS (BB_CWARPS * 32)
@@ -87,10 +88,23 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
     return n_real >= 1 ? base : -1;
 }
 
-// Occupancy against spills (measured): 3 CTAs/SM = 80 registers with ~70 B of spills, 4 CTAs/SM =
-// 64 registers with ~170 B.  On the KITTI-shaped image (1872 tiles) 3 is 5 % faster, on the 1080p-class images
-// (8160 / 9600 tiles, deep lists) 4 is 7-9 % faster; 2 CTAs/SM (112 registers, no spills) loses everywhere.  Both are
-// instantiated and the launcher picks by tile count.
+// Occupancy against spills (measured): 3 CTAs/SM = 80 registers, 4 CTAs/SM = 64 registers.  On the
+// KITTI-shaped image (1872 tiles) 3 is 5 % faster, on the 1080p-class images (8160 / 9600 tiles, deep lists) 4 is 7-9 %
+// faster; 2 CTAs/SM (112 registers, no spills) loses everywhere.  Both are instantiated and the launcher picks by tile
+// count.
+//
+// What ptxas spilled were the per-pixel CONSTANTS of the gradient arithmetic (the pixel's upstream gradients and final
+// T / M1 / distortion): 6 local-memory loads per blended pair and one per bucket start, the latter alone 13 % of the
+// kernel's stall samples (profiles/r02_blend_backward_lines.txt, line `ar_reg = reg_f - fin_reg`).  They now live in
+// shared memory, [k][thread] (conflict-free), read once per use: all 10 of them at 3 CTAs/SM (spills 72 -> 24 B, none
+// left in the per-pair path; -3.7 % at C2), the first 5 at 4 CTAs/SM, where shared memory is what limits the L1 that
+// catches the remaining spills (5: -2.2 % at C4 / C5; 10: +14..17 %).  profiles/r02_ab_variants.txt, block r02j.
+#ifndef BB_PIX_N3
+#define BB_PIX_N3 10
+#endif
+#ifndef BB_PIX_N4
+#define BB_PIX_N4 5
+#endif
 #ifndef BB_DEEP_TILES
 #define BB_DEEP_TILES 4000
 #endif
@@ -111,6 +125,11 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     __shared__ uint32_t s_done[BB_STAGES];
     __shared__ uint32_t s_maxlast[BB_CWARPS];
     __shared__ float s_shadow[9][BB_THREADS];  // forward-state shadow of the Q4 case: ar[8], T
+    // per-pixel constants of the gradient arithmetic (see above): 0..2 dLn, 3 M1_final, 4 fin_reg, 5 bg . dL_dpixel,
+    // 6 dLa, 7 dLd, 8 dLreg, 9 T_final; the first PIX_N of them live here, the rest stay in registers
+    constexpr int PIX_N = MIN_CTAS >= 4 ? BB_PIX_N4 : BB_PIX_N3;
+    extern __shared__ float s_pix_dyn[];
+    float(*s_pix)[BB_THREADS] = (float(*)[BB_THREADS])s_pix_dyn;
 
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
 #ifdef SB_DEBUG_NO_LPT
@@ -160,6 +179,13 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     float bg_dot_dpixel = 0.0f;
 #pragma unroll
     for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += bg[ch] * dLc[ch];
+    {
+        const float pv[10] = {dLn[0], dLn[1], dLn[2], M1_final, fin_reg, bg_dot_dpixel, dLa, dLd, dLreg, T_final};
+#pragma unroll
+        for (int k = 0; k < PIX_N; k++) s_pix[k][tid] = pv[k];
+    }
+    const volatile float* pixc = &s_pix[0][tid];   // volatile: one LDS per use below, nothing hoisted back into registers
+#define BB_PIX(k, reg) ((k) < PIX_N ? pixc[(k) * BB_THREADS] : (reg))
 
     // tile-wide max of `last` bounds the walk (reference: max_contrib bucket skip, backward.cu:503-505);
     // each warp blends only up to its own max
@@ -228,7 +254,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                 for (int i = 0; i < 8; i++) ar[i] = s_shadow[i][tid];
                 div = false;
             }
-            ar_reg = reg_f - fin_reg;
+            ar_reg = reg_f - BB_PIX(4, fin_reg);
             M1b = M1;
             M2b = M2;
             const float4(*sr)[SB_REC_F4] = s_rec[st];
@@ -313,6 +339,10 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                             hit = true;
                             const float dmd_dd = __fdividef((SB_FAR * SB_NEAR) / (SB_FAR - SB_NEAR), c_d * c_d);
                             // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
+                            const float dLn_[3] = {BB_PIX(0, dLn[0]), BB_PIX(1, dLn[1]), BB_PIX(2, dLn[2])};
+                            const float dLd_ = BB_PIX(7, dLd), dLa_ = BB_PIX(6, dLa), dLreg_ = BB_PIX(8, dLreg);
+                            const float T_final_ = BB_PIX(9, T_final), M1_final_ = BB_PIX(3, M1_final);
+                            const float bg_dot_ = BB_PIX(5, bg_dot_dpixel);
                             const float dchannel_dcolor = alpha * T;
                             const float inv1ma = __fdividef(1.0f, 1.0f - alpha);  // alpha <= 0.99
                             float dL_dalpha = 0.0f;
@@ -323,26 +353,26 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                                 dL_dalpha += ((c[ch] * T) - inv1ma * (-ar[ch])) * dLc[ch];
                                 g[19] += fabsf(dchannel_dcolor * dLc[ch]);
                             }
-                            dL_dalpha += (-T_final * inv1ma) * bg_dot_dpixel;
+                            dL_dalpha += (-T_final_ * inv1ma) * bg_dot_;
                             g[18] = dchannel_dcolor;
                             float dL_dz = 0.0f;
                             ar[3] += T * alpha * c_d;
-                            dL_dalpha += ((c_d * T) - inv1ma * (-ar[3])) * dLd;
-                            dL_dz += alpha * T * dLd;
+                            dL_dalpha += ((c_d * T) - inv1ma * (-ar[3])) * dLd_;
+                            dL_dz += alpha * T * dLd_;
                             ar[4] += T * alpha * 1.0f;
-                            dL_dalpha += ((1.0f * T) - inv1ma * (-ar[4])) * dLa;
+                            dL_dalpha += ((1.0f * T) - inv1ma * (-ar[4])) * dLa_;
 #pragma unroll
                             for (int ch = 0; ch < 3; ch++) {
                                 ar[5 + ch] += T * alpha * nrm[ch];
-                                g[11 + ch] = dchannel_dcolor * dLn[ch];
-                                dL_dalpha += ((nrm[ch] * T) - inv1ma * (-ar[5 + ch])) * dLn[ch];
+                                g[11 + ch] = dchannel_dcolor * dLn_[ch];
+                                dL_dalpha += ((nrm[ch] * T) - inv1ma * (-ar[5 + ch])) * dLn_[ch];
                             }
                             const float A = 1 - T;
                             const float dist = (m_d * m_d * A + M2b - 2 * m_d * M1b);
                             ar_reg += T * alpha * dist;
-                            dL_dalpha += ((dist * T) - inv1ma * (-ar_reg)) * dLreg;
-                            const float final_A = 1 - T_final;
-                            const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - M1_final) * dLreg;
+                            dL_dalpha += ((dist * T) - inv1ma * (-ar_reg)) * dLreg_;
+                            const float final_A = 1 - T_final_;
+                            const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - M1_final_) * dLreg_;
                             dL_dz += dL_dmd * dmd_dd;
                             T *= (1.0f - alpha);
 
@@ -403,8 +433,23 @@ int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, co
                              float* grad_acc, const uint32_t* hit_masks, const uint32_t* walk_cap, cudaStream_t s) {
     SbImageLayout IL = sb_image_layout(W, H);
     const int grid_x = (W + SB_TILE_X - 1) / SB_TILE_X, grid_y = (H + SB_TILE_Y - 1) / SB_TILE_Y;
-    auto kern = grid_x * grid_y >= BB_DEEP_TILES ? sb_blend_backward_kernel<4> : sb_blend_backward_kernel<3>;
-    kern<<<grid_x * grid_y, BB_THREADS, 0, s>>>(
+    const bool deep = grid_x * grid_y >= BB_DEEP_TILES;
+    const size_t dyn = (size_t)(deep ? BB_PIX_N4 : BB_PIX_N3) * BB_THREADS * sizeof(float);
+    {   // static + dynamic shared memory passes 48 KB: opt in, once per device (function attributes are per device)
+        static std::mutex mu;
+        static bool attr_set[SB_MAX_DEVICES] = {};
+        const int dev = sb_current_device();
+        std::lock_guard<std::mutex> lock(mu);
+        if (!attr_set[dev]) {
+            SB_CUDA_CHECK(cudaFuncSetAttribute(sb_blend_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               BB_PIX_N3 * BB_THREADS * (int)sizeof(float)));
+            SB_CUDA_CHECK(cudaFuncSetAttribute(sb_blend_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                               BB_PIX_N4 * BB_THREADS * (int)sizeof(float)));
+            attr_set[dev] = true;
+        }
+    }
+    auto kern = deep ? sb_blend_backward_kernel<4> : sb_blend_backward_kernel<3>;
+    kern<<<grid_x * grid_y, BB_THREADS, dyn, s>>>(
         W, H, grid_x, (const uint2*)(image + IL.ranges), (const uint32_t*)(image + IL.order), point_list, (const float4*)geom, bg,
         (const float*)(image + IL.final_T), (const uint32_t*)(image + IL.n_contrib), out_color, out_others,
         dL_dcolor, dL_dothers, pixel_mask, grad_acc, hit_masks, walk_cap);
