@@ -96,11 +96,11 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
 // What ptxas spilled were the per-pixel CONSTANTS of the gradient arithmetic (the pixel's upstream gradients and final
 // T / M1 / distortion): 6 local-memory loads per blended pair and one per bucket start, the latter alone 13 % of the
 // kernel's stall samples (profiles/r02_blend_backward_lines.txt, line `ar_reg = reg_f - fin_reg`).  They now live in
-// shared memory, [k][thread] (conflict-free), read once per use: all 10 of them at 3 CTAs/SM (spills 72 -> 24 B, none
+// shared memory, [k][thread] (conflict-free), read once per use: all 13 of them at 3 CTAs/SM (spills 72 -> 12 B, none
 // left in the per-pair path; -3.7 % at C2), the first 5 at 4 CTAs/SM, where shared memory is what limits the L1 that
-// catches the remaining spills (5: -2.2 % at C4 / C5; 10: +14..17 %).  profiles/r02_ab_variants.txt, block r02j.
+// catches the remaining spills (5: -3.3 % at C4 / C5; 7 or 10: +11..17 %).  profiles/r02_ab_variants.txt, blocks r02j-l.
 #ifndef BB_PIX_N3
-#define BB_PIX_N3 10
+#define BB_PIX_N3 13
 #endif
 #ifndef BB_PIX_N4
 #define BB_PIX_N4 5
@@ -126,7 +126,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     __shared__ uint32_t s_maxlast[BB_CWARPS];
     __shared__ float s_shadow[9][BB_THREADS];  // forward-state shadow of the Q4 case: ar[8], T
     // per-pixel constants of the gradient arithmetic (see above): 0..2 dLn, 3 M1_final, 4 fin_reg, 5 bg . dL_dpixel,
-    // 6 dLa, 7 dLd, 8 dLreg, 9 T_final; the first PIX_N of them live here, the rest stay in registers
+    // 6 dLa, 7 dLd, 8 dLreg, 9 T_final, 10..12 dLc; the first PIX_N of them live here, the rest stay in registers
     constexpr int PIX_N = MIN_CTAS >= 4 ? BB_PIX_N4 : BB_PIX_N3;
     extern __shared__ float s_pix_dyn[];
     float(*s_pix)[BB_THREADS] = (float(*)[BB_THREADS])s_pix_dyn;
@@ -180,7 +180,8 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #pragma unroll
     for (int ch = 0; ch < 3; ch++) bg_dot_dpixel += bg[ch] * dLc[ch];
     {
-        const float pv[10] = {dLn[0], dLn[1], dLn[2], M1_final, fin_reg, bg_dot_dpixel, dLa, dLd, dLreg, T_final};
+        const float pv[13] = {dLn[0], dLn[1], dLn[2], M1_final, fin_reg, bg_dot_dpixel, dLa, dLd, dLreg, T_final,
+                              dLc[0], dLc[1], dLc[2]};
 #pragma unroll
         for (int k = 0; k < PIX_N; k++) s_pix[k][tid] = pv[k];
     }
@@ -340,6 +341,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
                             const float dmd_dd = __fdividef((SB_FAR * SB_NEAR) / (SB_FAR - SB_NEAR), c_d * c_d);
                             // ---- the reference's gradient arithmetic (backward.cu:696-814) ----
                             const float dLn_[3] = {BB_PIX(0, dLn[0]), BB_PIX(1, dLn[1]), BB_PIX(2, dLn[2])};
+                            const float dLc_[3] = {BB_PIX(10, dLc[0]), BB_PIX(11, dLc[1]), BB_PIX(12, dLc[2])};
                             const float dLd_ = BB_PIX(7, dLd), dLa_ = BB_PIX(6, dLa), dLreg_ = BB_PIX(8, dLreg);
                             const float T_final_ = BB_PIX(9, T_final), M1_final_ = BB_PIX(3, M1_final);
                             const float bg_dot_ = BB_PIX(5, bg_dot_dpixel);
@@ -349,9 +351,9 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #pragma unroll
                             for (int ch = 0; ch < 3; ch++) {
                                 ar[ch] += T * alpha * c[ch];
-                                g[15 + ch] = dchannel_dcolor * dLc[ch];
-                                dL_dalpha += ((c[ch] * T) - inv1ma * (-ar[ch])) * dLc[ch];
-                                g[19] += fabsf(dchannel_dcolor * dLc[ch]);
+                                g[15 + ch] = dchannel_dcolor * dLc_[ch];
+                                dL_dalpha += ((c[ch] * T) - inv1ma * (-ar[ch])) * dLc_[ch];
+                                g[19] += fabsf(dchannel_dcolor * dLc_[ch]);
                             }
                             dL_dalpha += (-T_final_ * inv1ma) * bg_dot_;
                             g[18] = dchannel_dcolor;
