@@ -1,4 +1,5 @@
-"""CPU: the warp-level block cull of the blend kernels (csrc/pair_math.cuh::sb_block_culled) is conservative.
+"""CPU: the warp-level block culls of the forward blend (csrc/pair_math.cuh::sb_block_far -- the interval form the kernel
+uses -- and the opt-in exact form sb_block_culled) are conservative.
 
 A float32 numpy port of sb_cull_data / the lane-level test / sb_block_culled is run on the surfels of the
 synthetic scenes (T matrices from the oracle's preprocess) against every 8x4 pixel block around each surfel:
@@ -77,6 +78,92 @@ def block_culled(A, B, C, tau, xy, bx0, bx1, by0, by1):
         sx, sy = ((b * e - f32(2) * c * d) / det).astype(f32), ((b * d - f32(2) * a * e) / det).astype(f32)
         centre_in = (sx >= xl) & (sx <= xh) & (sy >= yl) & (sy <= yh)
         return disc_out & ellipse & ~centre_in & (m > margin)
+
+
+def block_far(A, B, C, tau, xy, bx0, by0):
+    """pair_math.cuh::sb_block_far for the 8x4 block whose first pixel is (bx0, by0); same operation order, float32"""
+    with np.errstate(all="ignore"):
+        dxc, dyc = (xy[:, 0] - (bx0 + f32(3.5))).astype(f32), (xy[:, 1] - (by0 + f32(1.5))).astype(f32)
+        adx, ady = np.abs(dxc), np.abs(dyc)
+        nx, ny = np.maximum(adx - f32(3.5), f32(0)), np.maximum(ady - f32(1.5), f32(0))
+        r2 = (nx * nx + ny * ny).astype(f32)
+        disc_out = (r2 + r2) > tau * f32(1.0001) + f32(1e-4)
+        b = []
+        for i in range(3):
+            q = (C[:, i] + A[:, i] * dxc + B[:, i] * dyc).astype(f32)
+            r = (f32(3.5) * np.abs(A[:, i]) + f32(1.5) * np.abs(B[:, i])).astype(f32)
+            g = (np.abs(C[:, i]) + np.abs(A[:, i]) * adx + np.abs(B[:, i]) * ady + r).astype(f32)
+            r = (r + f32(2e-6) * g).astype(f32)
+            b.append(np.maximum(np.abs(q) - r, f32(0)) if i < 2 else (np.abs(q) + r).astype(f32))
+        far = (b[0] * b[0] + b[1] * b[1]).astype(f32) > (f32(1.0001) * tau * (b[2] * b[2])).astype(f32)
+        return disc_out & far
+
+
+def _cull_inputs(cfg, P, W=None, H=None, view=-1):
+    scene, views = synthetic.make_scene(cfg, P=P, W=W, H=H)
+    inp = synthetic.view_inputs(scene, views[view])
+    pre = emu.preprocess(inp["means3D"], inp["scales"], inp["rotations"], inp["opacities"], inp["viewmatrix"],
+                         inp["projmatrix"], inp["W"], inp["H"])
+    vis = pre["visible"].numpy()
+    T = pre["T"].numpy().astype(f32)[vis]
+    xy = pre["means2D"].numpy().astype(f32)[vis]
+    opa = inp["opacities"].numpy().astype(f32).reshape(-1)[vis]
+    A, B, C, tau = cull_data(T[:, 0], T[:, 1], T[:, 2], xy, opa)
+    return A, B, C, tau, xy, pre["radii"].numpy()[vis], inp["W"], inp["H"]
+
+
+@pytest.mark.parametrize("cfg,P", [("C1", 4000), ("C3", 4000), ("C2", 4000)])
+def test_block_far_never_drops_a_passing_pixel(cfg, P):
+    """every block of the 8x4 lattice within +-5 blocks in x and +-10 in y of each surfel's screen centre"""
+    A, B, C, tau, xy, _, _, _ = _cull_inputs(cfg, P, 320, 240)
+    n = len(xy)
+    assert n > 500
+    lx, ly = np.arange(8, dtype=f32), np.arange(4, dtype=f32)
+    cbx, cby = np.floor(xy[:, 0] / 8), np.floor(xy[:, 1] / 4)
+    far_blocks = missed = 0
+    for ox in range(-5, 6):
+        for oy in range(-10, 11):
+            bx0, by0 = ((cbx + ox) * 8).astype(f32), ((cby + oy) * 4).astype(f32)
+            bf = block_far(A, B, C, tau, xy, bx0, by0)
+            px = (bx0[:, None] + np.tile(lx, 4)[None, :]).astype(f32)
+            py = (by0[:, None] + np.repeat(ly, 8)[None, :]).astype(f32)
+            lc = lane_culled(A, B, C, tau, xy, px, py)
+            bad = bf & ~lc.all(1)
+            assert not bad.any(), (cfg, ox, oy, int(bad.sum()))
+            far_blocks += int(bf.sum())
+            missed += int((~bf & lc.all(1)).sum())  # visited although every lane rejects
+    total = n * 11 * 21
+    assert far_blocks > 0.5 * total, (far_blocks, total)   # not vacuous: most far blocks are skipped ...
+    assert missed < 0.2 * total, (missed, total)           # ... and few all-rejecting blocks are still visited
+
+
+def test_block_far_on_surfels_that_cross_the_camera_plane():
+    """The side-looking rig camera of C5: surfels just beyond the near plane have footprints that are hyperbolae,
+    unbounded boxes and screen centres thousands of pixels away (they own half of that config's pairs).  Every third
+    8x4 block of the full 1920x1280 screen against each of them."""
+    A, B, C, tau, xy, radii, W, H = _cull_inputs("C5", 400_000)
+    big = np.argsort(-radii.astype(np.int64))[:250]
+    assert radii[big].min() > 200
+    A, B, C, tau, xy = A[big], B[big], C[big], tau[big], xy[big]
+    lx, ly = np.tile(np.arange(8, dtype=f32), 4), np.repeat(np.arange(4, dtype=f32), 8)
+    blocks = far = cullable = 0
+    for by in range(0, H // 4, 3):
+        bx0 = (np.arange(0, W // 8, 3) * 8).astype(f32)
+        # [surfel, block] -> flatten
+        S, Bn = len(xy), len(bx0)
+        rep = lambda v: np.repeat(v, Bn, axis=0)
+        bx = np.tile(bx0, S)
+        byv = np.full(S * Bn, by * 4, dtype=f32)
+        Ar, Br, Cr, tr, xr = rep(A), rep(B), rep(C), rep(tau), rep(xy)
+        bf = block_far(Ar, Br, Cr, tr, xr, bx, byv)
+        lc = lane_culled(Ar, Br, Cr, tr, xr, (bx[:, None] + lx[None, :]).astype(f32), (byv[:, None] + ly[None, :]).astype(f32))
+        bad = bf & ~lc.all(1)
+        assert not bad.any(), (by, int(bad.sum()))
+        blocks += len(bf)
+        far += int(bf.sum())
+        cullable += int(lc.all(1).sum())
+    assert cullable > 0.5 * blocks                      # these footprints miss most of the screen ...
+    assert far > 0.95 * cullable, (far, cullable)       # ... and the interval test finds nearly all of it
 
 
 @pytest.mark.parametrize("cfg,P", [("C1", 4000), ("C3", 4000), ("C2", 4000)])

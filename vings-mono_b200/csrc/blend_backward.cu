@@ -29,7 +29,8 @@
 //     candidate (18 % of this kernel's instructions in round 1, profiles/r01_final_blend_backward_lines.txt) are
 //     gone.  A pixel joins a visit iff the surfel lies before its last contributor; every gate is then the
 //     reference's own arithmetic, so a pixel outside the surfel's footprint fails alpha >= 1/255 exactly as it does
-//     in the reference, which evaluates all 256 pixels of a tile for every surfel.
+//     in the reference, which evaluates all 256 pixels of a tile for every surfel.  The ring's fill in turn gathers
+//     only the records of surfels whose bit is set in SOME warp's word (BB_SPARSE_FILL).
 #include "pair_math.cuh"
 #include "ring.cuh"
 #include <mutex>
@@ -104,6 +105,12 @@ __device__ __forceinline__ int butterfly_slot(int lane, int K) {
 #endif
 #ifndef BB_PIX_N4
 #define BB_PIX_N4 5
+#endif
+// The ring gathers only the records some warp of the tile will visit (the union of the batch's 8 hit masks).  Measured
+// (profiles/r02_ab_variants.txt, block r02m): C2 1.143 -> 1.133 ms, C4 3.90 -> 3.17, C5 5.28 -> 4.03 -- on the
+// 1080p-class configs 4 of 5 list entries are surfels whose footprint misses the whole tile.
+#ifndef BB_SPARSE_FILL
+#define BB_SPARSE_FILL 1
 #endif
 #ifndef BB_DEEP_TILES
 #define BB_DEEP_TILES 4000
@@ -215,16 +222,31 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     auto fill = [&](int b) {
         const int st = b % BB_STAGES;
         const int cnt = min(BB_BATCH, n_walk - b * BB_BATCH);
+        uint32_t mw = 0;
+        if (lane < BB_CWARPS) {
+            mw = __ldg(tile_masks + (size_t)b * BB_CWARPS + lane);
+            s_mask[st][lane] = mw;
+        }
+#if BB_SPARSE_FILL
+        // only the surfels some warp of the tile will visit are gathered (the union of the 8 hit masks): on the
+        // 1080p-class configs 4 of 5 list entries are surfels whose footprint misses the whole tile
+        const uint32_t want = __reduce_or_sync(0xffffffffu, mw) & (cnt < BB_BATCH ? (1u << cnt) - 1u : 0xffffffffu);
+#else
+        const uint32_t want = cnt < BB_BATCH ? (1u << cnt) - 1u : 0xffffffffu;
+#endif
+        const bool mine = (want >> lane) & 1u;
         uint32_t id = 0;
-        if (lane < cnt) {
+        if (mine) {
             id = __ldg(point_list + range.x + b * BB_BATCH + lane);
             s_id[st][lane] = id;
         }
-        if (lane < BB_CWARPS) s_mask[st][lane] = __ldg(tile_masks + (size_t)b * BB_CWARPS + lane);
         __syncwarp();
-        if (lane == 0) bb_mbar_expect_tx(&s_full[st], (uint32_t)cnt * (SB_REC_F4 * 16));
+        if (lane == 0) {
+            if (want) bb_mbar_expect_tx(&s_full[st], (uint32_t)__popc(want) * (SB_REC_F4 * 16));
+            else bb_mbar_arrive(&s_full[st]);   // nothing to wait for: the phase completes at once
+        }
         __syncwarp();
-        if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
+        if (mine) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
     };
     for (int b0 = wid; b0 < BB_STAGES && b0 < nbatches; b0 += BB_CWARPS) fill(b0);  // prime the ring
     const int my_walk = min(n_walk, (int)wmax);   // this warp's pixels blend nothing at or behind this list position

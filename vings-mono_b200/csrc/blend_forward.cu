@@ -27,6 +27,19 @@
 #ifndef FB_POLL_NS
 #define FB_POLL_NS 200   // measured (C5 forward -3 %, C2 neutral): see the wait loop
 #endif
+// Warp-level interval cull (pair_math.cuh::sb_block_far) behind the box test: the lane that owns a surfel of the batch
+// also bounds the lane-level test over the warp's whole 8x4 block.  On the CPU model of the walk (tests/
+// test_block_cull_cpu.py, tools/forward_walk_model.py) it removes 46 % (C2), 74 % (C4) and 92 % (C5) of the
+// box-passing (warp, surfel) visits -- all of which phase 1 would reject pixel by pixel; on the 1080p-class configs
+// half of all pairs belong to < 1 % of the surfels, the ones that cross the camera plane: unbounded boxes, every tile.
+#ifndef FB_BLOCK_FAR
+#define FB_BLOCK_FAR 1
+#endif
+// float4s per ring slot: the 8 of the record + 1 of padding, so that the per-lane record reads of the warp-level cull
+// (lane = surfel: row stride 144 B) spread over all bank groups instead of hitting one 32 ways
+#ifndef FB_REC_PITCH
+#define FB_REC_PITCH 9
+#endif
 
 // (a min-CTAs bound of 4/5/6 -> 56/48/40 registers was measured 2-5 % slower than the unconstrained 58)
 __global__ void __launch_bounds__(FB_THREADS)
@@ -34,7 +47,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
                         const uint32_t* __restrict__ point_list, const float4* __restrict__ rec,
                         const float* __restrict__ bg, float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
                         float* __restrict__ out_color, float* __restrict__ out_others, uint32_t* __restrict__ hit_masks) {
-    __shared__ __align__(128) float4 s_rec[FB_STAGES][FB_BATCH][SB_REC_F4];
+    __shared__ __align__(128) float4 s_rec[FB_STAGES][FB_BATCH][FB_REC_PITCH];
     __shared__ __align__(8) uint64_t s_full[FB_STAGES];
     __shared__ uint32_t s_cnt[FB_STAGES];
     __shared__ uint32_t s_donemask;  // warps whose 32 pixels have all terminated
@@ -54,6 +67,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float2 pixf = {(float)px, (float)py};
     const float bx0 = (float)wx0, bx1 = (float)(wx0 + 7), by0 = (float)wy0, by1 = (float)(wy0 + 3);
+    const float bcx = (float)wx0 + 3.5f, bcy = (float)wy0 + 1.5f;   // block centre (sb_block_far)
     bool done = !inside;
 
     const uint2 range = ranges[tile];
@@ -108,7 +122,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         }
         if (stop) break;
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
-        const float4(*sq)[SB_REC_F4] = s_rec[st];
+        const float4(*sq)[FB_REC_PITCH] = s_rec[st];
         if (!wdone) {
             const int c = 0;
             // ---- warp-level cull: lane tests surfel c+lane's box against the warp's pixel block ----
@@ -121,6 +135,9 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
             if (c + lane < cnt) {
                 const float4 bb = sq[c + lane][SB_REC_BBOX];
                 ov = bb.x <= bx1 && bb.y >= bx0 && bb.z <= by1 && bb.w >= by0;
+#if FB_BLOCK_FAR
+                if (ov) ov = !sb_block_far(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bcx, bcy);
+#endif
 #ifdef SB_BLOCK_CULL  // opt-in: measured neutral
                 if (ov) ov = !sb_block_culled(sq[c + lane][0], sq[c + lane][1], sq[c + lane][2], bx0, bx1, by0, by1);
 #endif

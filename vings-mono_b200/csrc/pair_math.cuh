@@ -59,7 +59,41 @@ __device__ __forceinline__ float sb_ndc_depth(float depth) {
     return __fmul_rn(__fadd_rn(__fdiv_rn(-SB_NEAR, depth), 1.0f), SB_FAR / (SB_FAR - SB_NEAR));
 }
 
-// ---- warp-level cull: can a whole pixel block skip a surfel? ----
+// ---- warp-level cull, interval form: can a whole 8x4 pixel block skip a surfel? ----
+// One lane answers for ONE surfel and the warp's whole block (centre (bcx, bcy), pixel centres within +-3.5 / +-1.5 of
+// it).  q = C + A d.x + B d.y is affine in the pixel, so over the block every component lies in an interval around its
+// value at the block centre:  |q_i - q_i(centre)| <= r_i = 3.5 |A_i| + 1.5 |B_i|.  Then
+//      E = q.x^2 + q.y^2 - tau q.z^2  >=  max(|q.x| - r.x, 0)^2 + max(|q.y| - r.y, 0)^2 - tau (|q.z| + r.z)^2
+// and the block is skipped when that bound is positive and the rectangle's nearest point to the surfel's centre is
+// outside the low-pass disc -- i.e. when the lane-level test would reject all 32 pixels.  Unlike sb_block_culled below
+// this holds for ANY form (ellipse, hyperbola of a surfel that crosses the camera plane -- their boxes are unbounded and
+// they are the bulk of the pairs of the 1080p-class configs), needs no division, and is centred on the block, so its
+// slack does not grow with the distance to a far-away surfel centre.
+// Rounding: the lane-level test sees q with an error of a few ulps of G_i = |C_i| + |A_i d.x| + |B_i d.y| (the terms
+// cancel for far-away centres); every interval is widened by 2e-6 G_i (~33 ulps), and the final comparison carries a
+// relative 1e-4 for the rounding of the three squares.  NaNs compare false: the block is visited.
+// CPU model + conservativeness test against the lane-level test: tests/test_block_cull_cpu.py.
+__device__ __forceinline__ bool sb_block_far(float4 c0, float4 c1, float4 c2, float bcx, float bcy) {
+    const float tau = c2.w;
+    const float dxc = c0.w - bcx, dyc = c1.w - bcy;   // d = xy - pixel at the block centre
+    const float adx = fabsf(dxc), ady = fabsf(dyc);
+    const float nx = fmaxf(adx - 3.5f, 0.0f), ny = fmaxf(ady - 1.5f, 0.0f);
+    const float r2 = nx * nx + ny * ny;
+    if (!((r2 + r2) > tau * 1.0001f + 1e-4f)) return false;  // the low-pass disc reaches the block
+    const float Av[3] = {c0.x, c0.y, c0.z}, Bv[3] = {c1.x, c1.y, c1.z}, Cv[3] = {c2.x, c2.y, c2.z};
+    float b[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        const float q = Cv[i] + Av[i] * dxc + Bv[i] * dyc;
+        float r = 3.5f * fabsf(Av[i]) + 1.5f * fabsf(Bv[i]);
+        const float g = fabsf(Cv[i]) + fabsf(Av[i]) * adx + fabsf(Bv[i]) * ady + r;
+        r += 2e-6f * g;
+        b[i] = (i < 2) ? fmaxf(fabsf(q) - r, 0.0f) : fabsf(q) + r;
+    }
+    return (b[0] * b[0] + b[1] * b[1]) > 1.0001f * tau * (b[2] * b[2]);
+}
+
+// ---- warp-level cull, exact form (opt-in, -DSB_BLOCK_CULL; ellipses only): can a whole pixel block skip a surfel? ----
 // The lane-level test of the blend kernels rejects pixel (px,py) iff  E(d) > 0  &&  2|d|^2 > tau  with
 // d = xy - pixel and E(d) = q.x^2 + q.y^2 - tau q.z^2, q = C + A d.x + B d.y (record quads 0-2).  One lane
 // evaluates this for ONE surfel against the warp's whole block [bx0,bx1] x [by0,by1] (pixel centres, inclusive):
