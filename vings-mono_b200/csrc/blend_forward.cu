@@ -5,14 +5,17 @@
 // The kernel is instruction-issue bound, not HBM bound (profiles/): ~90 % of the (pixel, surfel)
 // pairs a tile list implies contribute nothing, so the design goal is to reject those pairs with as
 // few issued instructions as possible while running the reference's exact arithmetic on the rest:
-//   1. the sorted surfel *records* (128 B = one line, packed once by the preprocess kernel) are
-//      gathered with cp.async 16-B copies into a double-buffered shared-memory ring, so the gather of
-//      batch b+1 overlaps the blend of batch b (the reference does 4 scattered array reads plus a
-//      per-pixel global colour read per pair);
-//   2. warp-level cull: each lane tests ONE surfel's conservative pixel box against the warp's 8x4
-//      block, a ballot compacts the survivors, and only those are visited (1 test per 32 pairs);
+//   1. the sorted surfel *records* (128 B = one line, packed once by the preprocess kernel) are gathered with one
+//      cp.async.bulk (TMA engine, 1-D) per surfel into an 8-stage shared-memory ring of 32-surfel batches handed
+//      over by mbarriers (ring.cuh), so the gathers run up to 8 batches ahead of the blend and the warps of a CTA
+//      never meet at a barrier inside the walk (the reference does 4 scattered array reads plus a per-pixel global
+//      colour read per pair, behind two CTA barriers per 256 surfels);
+//   2. warp-level cull: each lane tests ONE surfel of the batch against the warp's 8x4 block -- its conservative
+//      pixel box, then an interval bound of the lane-level test over the whole block (sb_block_far) -- a ballot
+//      compacts the survivors, and only those are visited (1 test per 32 pairs);
 //   3. lane-level cull: a division-free test (6 FFMA for the affine ray-splat cross product + a conic
-//      compare) rejects pixels outside the surfel's alpha >= 1/255 footprint (surfel_math.cuh);
+//      compare) rejects pixels outside the surfel's alpha >= 1/255 footprint (surfel_math.cuh); the OR of the
+//      lanes' pass bits is stored as the (batch, warp) hit mask the backward walks;
 //   4. pairs that pass run the reference's expression order, so the gates (alpha < 1/255,
 //      T < 1e-4, T > 0.5, rho3d <= rho2d, depth < near) flip on the same pairs;
 //   5. no per-32-splat checkpoints are written (the backward re-walks the tile instead), removing the
@@ -28,15 +31,17 @@
 #define FB_POLL_NS 200   // measured (C5 forward -3 %, C2 neutral): see the wait loop
 #endif
 // Warp-level interval cull (pair_math.cuh::sb_block_far) behind the box test: the lane that owns a surfel of the batch
-// also bounds the lane-level test over the warp's whole 8x4 block.  On the CPU model of the walk (tests/
-// test_block_cull_cpu.py, tools/forward_walk_model.py) it removes 46 % (C2), 74 % (C4) and 92 % (C5) of the
-// box-passing (warp, surfel) visits -- all of which phase 1 would reject pixel by pixel; on the 1080p-class configs
-// half of all pairs belong to < 1 % of the surfels, the ones that cross the camera plane: unbounded boxes, every tile.
+// also bounds the lane-level test over the warp's whole 8x4 block.  On the CPU model of the walk (tools/
+// forward_walk_model.py, profiles/r02_forward_walk_model.txt) it removes 69 % (C2), 29 % (C3), 94 % (C4) and 96 % (C5)
+// of the box-passing (warp, surfel) visits -- all of which phase 1 would reject pixel by pixel: on the 1080p-class
+// configs half of all pairs belong to < 1 % of the surfels, the ones that cross the camera plane (unbounded boxes,
+// every tile).  Measured (profiles/r02_ab_variants.txt, block r02m): C2 0.574 -> 0.489 ms, C4 5.48 -> 2.61, C5 7.66 -> 3.45.
 #ifndef FB_BLOCK_FAR
 #define FB_BLOCK_FAR 1
 #endif
 // float4s per ring slot: the 8 of the record + 1 of padding, so that the per-lane record reads of the warp-level cull
-// (lane = surfel: row stride 144 B) spread over all bank groups instead of hitting one 32 ways
+// (lane = surfel: row stride 144 B) spread over all bank groups instead of hitting one 32 ways.  With the 128-byte
+// pitch the same cull measures 0.542 (C2) and 6.71 ms (C5): the conflicts cost more than the cull saves.
 #ifndef FB_REC_PITCH
 #define FB_REC_PITCH 9
 #endif
