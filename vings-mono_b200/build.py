@@ -22,15 +22,18 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", 
 
 
 def csrc_hash():
-    """sha1 over the kernel sources and the ABI header: stamps profiles/traffic.json (tools/traffic_from_ncu.py) so
-    that bench.py can tell when an ncu capture predates the kernels it describes."""
+    """sha1 over the kernel sources and the ABI header with comments and whitespace stripped: stamps
+    profiles/traffic.json (tools/traffic_from_ncu.py) so that bench.py can tell when an ncu capture predates the kernels
+    it describes -- a comment-only edit does not invalidate a capture, any change of code does."""
     import hashlib
+    import re
+    strip = re.compile(r"/\*.*?\*/|//[^\n]*", re.S)
     h = hashlib.sha1()
     files = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
-    for f in files:
-        h.update(f.encode())
-        h.update(open(os.path.join(CSRC, f), "rb").read())
-    h.update(open(os.path.join(HERE, "..", "include", "surfel_b200.h"), "rb").read())
+    paths = [os.path.join(CSRC, f) for f in files] + [os.path.join(HERE, "..", "include", "surfel_b200.h")]
+    for path in paths:
+        h.update(os.path.basename(path).encode())
+        h.update("".join(strip.sub("", open(path).read()).split()).encode())
     return h.hexdigest()
 
 

@@ -12,12 +12,12 @@
 // Structure (round 2 of this kernel; profiles/r01_blend_backward_lines.txt showed 25 % of the stall samples
 // on the two CTA barriers per 32-surfel batch of the first version, with 59 % issue utilisation):
 //   * 8 warps (one 8x4 pixel block each, a thread owns a pixel) that never meet at a CTA barrier inside the walk;
-//   * the sorted surfels' 128-byte records are gathered with one cp.async.bulk (TMA engine, 1-D) per surfel
-//     into an 8-stage shared-memory ring of 32-surfel batches; a stage is handed to the warps by an mbarrier
-//     (expect_tx / complete_tx bytes) and handed back through a shared counter: the LAST warp to finish a
-//     batch refills its stage with the batch 8 ahead, so a warp waits only for data it needs and the warps
-//     drift up to 7 batches apart (a dedicated producer warp made 9 warps per CTA, which the four 16 K-register
-//     SM sub-partitions cannot hold twice at 112 registers: measured 1 CTA/SM and 3.0 ms);
+//   * the sorted surfels' 128-byte records are gathered (ring.cuh: 16-byte cp.async, or one TMA bulk copy per record
+//     with SB_RING_LDGSTS=0) into an 8-stage shared-memory ring of 32-surfel batches; a stage is handed to the warps
+//     by an mbarrier and handed back through a shared counter: the LAST warp to finish a batch refills its stage with
+//     the batch 8 ahead, so a warp waits only for data it needs and the warps drift up to 7 batches apart (a dedicated
+//     producer warp made 9 warps per CTA, which the four 16 K-register SM sub-partitions cannot hold twice at 112
+//     registers: measured 1 CTA/SM and 3.0 ms);
 //   * per hit surfel a 21-shuffle multi-value butterfly reduces the 20 gradient terms over the warp's 32
 //     pixels and 20 lanes issue ONE coalesced red.global.add.f32 over the surfel's 80-byte accumulation
 //     record (3 sectors); there is no cross-warp combine and no shared accumulation buffer;
@@ -202,7 +202,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
     for (int o = 16; o > 0; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
     if (lane == 0) s_maxlast[wid] = wmax;
     if (tid < BB_STAGES) {
-        bb_mbar_init(&s_full[tid], 1);
+        bb_mbar_init(&s_full[tid], BB_RING_ARRIVALS);
         s_done[tid] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -234,19 +234,13 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
 #else
         const uint32_t want = cnt < BB_BATCH ? (1u << cnt) - 1u : 0xffffffffu;
 #endif
-        const bool mine = (want >> lane) & 1u;
         uint32_t id = 0;
-        if (mine) {
+        if ((want >> lane) & 1u) {
             id = __ldg(point_list + range.x + b * BB_BATCH + lane);
             s_id[st][lane] = id;
         }
         __syncwarp();
-        if (lane == 0) {
-            if (want) bb_mbar_expect_tx(&s_full[st], (uint32_t)__popc(want) * (SB_REC_F4 * 16));
-            else bb_mbar_arrive(&s_full[st]);   // nothing to wait for: the phase completes at once
-        }
-        __syncwarp();
-        if (mine) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
+        bb_gather<SB_REC_F4>(s_rec[st], rec, id, want, &s_full[st], lane);
     };
     for (int b0 = wid; b0 < BB_STAGES && b0 < nbatches; b0 += BB_CWARPS) fill(b0);  // prime the ring
     const int my_walk = min(n_walk, (int)wmax);   // this warp's pixels blend nothing at or behind this list position
@@ -449,6 +443,7 @@ sb_blend_backward_kernel(int W, int H, int grid_x, const uint2* __restrict__ ran
             if (b + BB_STAGES < nbatches) fill(b + BB_STAGES);
         }
     }
+    bb_ring_drain();
 }
 
 int sb_launch_blend_backward(int W, int H, const float* bg, const char* geom, const uint32_t* point_list,

@@ -5,11 +5,12 @@
 // The kernel is instruction-issue bound, not HBM bound (profiles/): ~90 % of the (pixel, surfel)
 // pairs a tile list implies contribute nothing, so the design goal is to reject those pairs with as
 // few issued instructions as possible while running the reference's exact arithmetic on the rest:
-//   1. the sorted surfel *records* (128 B = one line, packed once by the preprocess kernel) are gathered with one
-//      cp.async.bulk (TMA engine, 1-D) per surfel into an 8-stage shared-memory ring of 32-surfel batches handed
-//      over by mbarriers (ring.cuh), so the gathers run up to 8 batches ahead of the blend and the warps of a CTA
-//      never meet at a barrier inside the walk (the reference does 4 scattered array reads plus a per-pixel global
-//      colour read per pair, behind two CTA barriers per 256 surfels);
+//   1. the sorted surfel *records* (128 B = one line, packed once by the preprocess kernel) are gathered by 16-byte
+//      cp.async (four whole records per warp instruction) into an 8-stage shared-memory ring of 32-surfel batches
+//      handed over by mbarriers (ring.cuh; the TMA bulk-copy gather it replaced is kept behind SB_RING_LDGSTS=0), so
+//      the gathers run up to 8 batches ahead of the blend and the warps of a CTA never meet at a barrier inside the
+//      walk (the reference does 4 scattered array reads plus a per-pixel global colour read per pair, behind two CTA
+//      barriers per 256 surfels);
 //   2. warp-level cull: each lane tests ONE surfel of the batch against the warp's 8x4 block -- its conservative
 //      pixel box, then an interval bound of the lane-level test over the whole block (sb_block_far) -- a ballot
 //      compacts the survivors, and only those are visited (1 test per 32 pairs);
@@ -83,7 +84,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
     uint32_t* my_masks = hit_masks + ((size_t)sb_hit_slot(range.x, tile) * FB_WARPS + wid);
 
     if (tid < FB_STAGES) {
-        bb_mbar_init(&s_full[tid], 1);
+        bb_mbar_init(&s_full[tid], BB_RING_ARRIVALS);
         s_cnt[tid] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -98,9 +99,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         const int cnt = min(FB_BATCH, n - b * FB_BATCH);
         uint32_t id = 0;
         if (lane < cnt) id = __ldg(point_list + range.x + b * FB_BATCH + lane);
-        if (lane == 0) bb_mbar_expect_tx(&s_full[st], (uint32_t)cnt * (SB_REC_F4 * 16));
-        __syncwarp();
-        if (lane < cnt) bb_bulk_g2s(&s_rec[st][lane][0], rec + (size_t)id * SB_REC_F4, SB_REC_F4 * 16, &s_full[st]);
+        bb_gather<FB_REC_PITCH>(s_rec[st], rec, id, cnt < FB_BATCH ? (1u << cnt) - 1u : 0xffffffffu, &s_full[st], lane);
     };
     for (int b0 = wid; b0 < FB_STAGES && b0 < nbatches; b0 += FB_WARPS) fill(b0);  // prime the ring
 
@@ -249,6 +248,7 @@ sb_blend_forward_kernel(int W, int H, int grid_x, const uint2* __restrict__ rang
         }
     }
 
+    bb_ring_drain();
     if (inside) {
         const size_t HW = (size_t)H * W;
         final_T[pix_id] = T;
