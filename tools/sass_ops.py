@@ -1,5 +1,5 @@
 """Counts of the Blackwell-specific SASS mnemonics per kernel of libsurfel_b200.so (cuobjdump -sass), the evidence
-behind DESIGN.md's "TMA bulk copies / mbarrier / redux / match" statements.
+behind DESIGN.md's "cp.async / TMA bulk copies / mbarrier / redux / match" statements.
 Usage: python tools/sass_ops.py > profiles/r02_sass_blackwell_ops.txt"""
 import os
 import re
@@ -9,7 +9,7 @@ from collections import Counter, OrderedDict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "vings-mono_b200", "diff_surfel_rasterization", "libsurfel_b200.so")
-OPS = ["UBLKCP", "UTMALDG", "SYNCS", "REDUX", "MATCH", "RED", "REDG", "ATOMG", "ATOMS", "SHFL", "VOTE", "MUFU", "LDS", "LDG",
+OPS = ["LDGSTS", "ARRIVES", "UBLKCP", "UTMALDG", "SYNCS", "REDUX", "MATCH", "RED", "REDG", "ATOMG", "ATOMS", "SHFL", "VOTE", "MUFU", "LDS", "LDG",
        "STG", "LDL", "STL", "UTCHMMA", "UTCQMMA", "HMMA"]
 
 
@@ -30,8 +30,9 @@ def main():
             kernels[cur][m.group(1)] += 1
             kernels[cur]["_total"] += 1
     print("# %s" % os.path.relpath(so, ROOT))
-    print("# cubin architectures: %s   (cuobjdump -sass | per-kernel mnemonic counts; UBLKCP = cp.async.bulk (TMA 1-D),"
+    print("# cubin architectures: %s   (cuobjdump -sass | per-kernel mnemonic counts; LDGSTS = cp.async 16 B global -> shared,"
           % ", ".join(archs))
+    print("#  ARRIVES = cp.async.mbarrier.arrive (LDGSTSBAR), UBLKCP = cp.async.bulk (TMA 1-D; the SB_RING_LDGSTS=0 build of the ring),")
     print("#  SYNCS = mbarrier ops, REDUX = warp redux.sync, MATCH = match.any; no UTMALDG / UTC*MMA / HMMA: no tensor tiles, no MMA)")
     used = [o for o in OPS if any(k[o] for k in kernels.values())]
     print("%-44s %7s " % ("kernel", "instr") + " ".join("%7s" % o for o in used))
