@@ -139,3 +139,44 @@ def test_synthetic_generators_are_deterministic_and_shaped():
     assert gt["rgb"].shape == (3, 376, 1241) and (gt["rgb"].sum(0) == 0).any() and (gt["depth"] > 0).all()
     # get_camera convention (scripts/gaussian/cameras.py:58-60): projmatrix = viewmatrix @ P^T, campos = c2w[:3,3]
     assert torch.allclose(v[0].campos, v[0].c2w[:3, 3].float(), atol=1e-5)
+
+
+def _build_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("sb200_build_t", os.path.join(ROOT, "vings-mono_b200", "build.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_csrc_hash_ignores_comments_and_sees_code(tmp_path, monkeypatch):
+    """The stamp of profiles/traffic.json (bench.py: roofline.traffic_stale): a comment or whitespace edit keeps an ncu
+    capture valid, any change of code invalidates it."""
+    import shutil
+    b = _build_module()
+    here = tmp_path / "pkg"
+    shutil.copytree(os.path.join(ROOT, "vings-mono_b200", "csrc"), here / "csrc",
+                    ignore=shutil.ignore_patterns("build*"))
+    os.makedirs(tmp_path / "include")
+    shutil.copy(os.path.join(ROOT, "include", "surfel_b200.h"), tmp_path / "include" / "surfel_b200.h")
+    monkeypatch.setattr(b, "HERE", str(here))
+    monkeypatch.setattr(b, "CSRC", str(here / "csrc"))
+    h0 = b.csrc_hash()
+    f = here / "csrc" / "ring.cuh"
+    src = f.read_text()
+    f.write_text("// a new comment\n" + src.replace("#pragma once", "#pragma once   /* spaced */\n"))
+    assert b.csrc_hash() == h0
+    f.write_text(src.replace("#define BB_RING_ARRIVALS 32", "#define BB_RING_ARRIVALS 31"))
+    assert b.csrc_hash() != h0
+
+
+def test_forward_walk_model_runs_and_finds_no_unsafe_cull(capsys, monkeypatch):
+    """tools/forward_walk_model.py (the CPU model behind DESIGN.md section 5) on three tiles of C1."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("fwm", os.path.join(ROOT, "tools", "forward_walk_model.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    monkeypatch.setattr(sys, "argv", ["forward_walk_model.py", "C1", "3"])
+    mod.main()
+    out = capsys.readouterr().out
+    assert "non-conservative culls: 0" in out and "model warp instructions per pair" in out
